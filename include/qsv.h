@@ -1,0 +1,163 @@
+/*
+ * qsv.h -- C ABI of the B200 statevector engine (libqsv.so).
+ *
+ * The reference (wanshoupu/quantum-simulations, package `quompiler`) is pure
+ * Python and has NO FFI of its own: its plug-in boundary for this path is the
+ * Python ABC `CircuitBuilder` (quompiler/circuits/qbuilder.py:9-49) driven by
+ * `QRenderer.render` (quompiler/circuits/render.py:12-32), and its arithmetic is
+ * dense numpy products (quompiler/construct/cgate.py:104-121,
+ * quompiler/construct/unitary.py:56-77).  Each entry point below therefore cites
+ * the reference code whose work it replaces.  The Python binding a maintainer
+ * would add on the reference side is a ctypes stub; see INTEGRATION.md.
+ *
+ * Conventions
+ *  - A state is a device array of `2^n_bits` complex amplitudes, interleaved
+ *    (re, im), complex128 (16 B) or complex64 (8 B), index bit 0 = least
+ *    significant.  A batch of 2^b states is stored batch-innermost, i.e. as ONE
+ *    array with n_bits = n_qubits + b whose low b bits no gate touches.
+ *  - Qubit at sorted-register position p of N owns logical bit N-1-p
+ *    (big-endian, quompiler/construct/qontroller.py:7-15); the caller adds b.
+ *  - Gate action (quompiler/construct/unitary.py:75-76 + qontroller.py:112-120):
+ *    for every index x with (x & ctrl_mask) == ctrl_value,
+ *        out[x | targets=r] = sum_c M[r][c] * in[x | targets=c],
+ *    M = matrix()*phase() row-major complex128, row/col bits taken over
+ *    target_bits[] with target_bits[0] the most significant.
+ *  - All pointers named `state`, `in`, `out`, `a`, `b` are DEVICE pointers owned
+ *    by the caller; `matrix`, `gates`, `pool`, `rows`, `perm` and every `out_*`
+ *    scalar are HOST pointers.  `stream` is a cudaStream_t passed as void*.
+ *  - Every function returns 0 on success or a negative QSV_E_* code; the message
+ *    is available from qsv_last_error().  No exception crosses the ABI.
+ *  - A context is bound to one device and is not thread-safe; use one context
+ *    per host thread / stream.
+ */
+#ifndef QSV_H
+#define QSV_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QSV_OK            0
+#define QSV_E_INVALID    -1   /* bad argument                                   */
+#define QSV_E_CUDA       -2   /* a CUDA runtime call failed                     */
+#define QSV_E_NOPROGRAM  -3   /* qsv_run before qsv_upload_program              */
+#define QSV_E_UNSUPPORTED -4  /* valid but not implemented for these sizes      */
+#define QSV_E_TOOBIG     -5   /* exceeds a documented fixed capacity            */
+
+#define QSV_C128 0
+#define QSV_C64  1
+
+/* gate kinds */
+#define QSV_DENSE1   0  /* controlled dense 2x2 on one target bit               */
+#define QSV_PERMX    1  /* controlled X: pure amplitude swap, no arithmetic     */
+#define QSV_DIAG1    2  /* controlled diag(d0,d1) on one target bit             */
+#define QSV_DENSEK   3  /* controlled dense 2^t x 2^t, 2 <= t <= QSV_MAX_TARGETS */
+#define QSV_ROWS2    4  /* two-level (Givens) unitary on rows row0,row1 of a
+                           [dim][batch] array; dim need not be a power of two   */
+
+#define QSV_MAX_TARGETS 5
+
+/* POD gate record, 64 bytes.  The flattened form of one CtrlGate
+ * (quompiler/construct/cgate.py:24-52) or two-level UnitaryM
+ * (quompiler/construct/unitary.py:26-46).                                       */
+typedef struct qsv_gate {
+    uint32_t kind;
+    uint32_t n_targets;
+    uint8_t  target_bits[8];   /* bit positions, most significant matrix bit first */
+    uint64_t ctrl_mask;
+    uint64_t ctrl_value;
+    uint64_t row0, row1;       /* QSV_ROWS2 only                                   */
+    uint64_t matrix_offset;    /* in complex128 elements into the matrix pool      */
+    uint64_t reserved;
+} qsv_gate_t;
+
+typedef struct qsv_stats {
+    uint64_t kernel_launches;  /* kernels of this library launched via this context */
+    uint64_t sweeps;           /* passes over the full state                        */
+    uint64_t amp_bytes;        /* algorithmic bytes: 2 * touched amplitudes * size  */
+    uint64_t gates_applied;    /* source gates executed                             */
+    uint64_t fused_sweeps;     /* sweeps executed by the fused tile kernel          */
+    uint64_t reserved[3];
+} qsv_stats_t;
+
+typedef struct qsv_ctx qsv_ctx;
+
+/* Library / context ------------------------------------------------------------ */
+const char* qsv_version(void);
+/* message of the last failure on `ctx` (or of the last failed qsv_create if NULL) */
+const char* qsv_last_error(const qsv_ctx* ctx);
+/* Creates a context on CUDA device `device` for amplitudes of type `dtype`.
+ * Allocates a small device scratch area (reduction partials, staged matrices).
+ * Replaces: nothing in the reference (numpy needs no context).                    */
+int  qsv_create(qsv_ctx** out, int device, int dtype);
+void qsv_destroy(qsv_ctx* ctx);
+int  qsv_get_stats(const qsv_ctx* ctx, qsv_stats_t* out);
+int  qsv_reset_stats(qsv_ctx* ctx);
+
+/* Single gates ------------------------------------------------------------------ */
+/* Applies one gate in place.  `matrix` = host complex128 row-major (2^t)^2 values
+ * (ignored for QSV_PERMX).  Replaces one factor of the dense product in
+ * CtrlGate.__matmul__ (quompiler/construct/cgate.py:104-121) together with the
+ * lifts it needs: expand/np.kron (cgate.py:195-218) and promote/ctrl_expand
+ * (cgate.py:307-331, quompiler/utils/inter_product.py:366-437) are implicit in the
+ * stride and control-mask index math.                                              */
+int qsv_apply_gate(qsv_ctx* ctx, void* state, int n_bits, const qsv_gate_t* gate,
+                   const double* matrix, void* stream);
+
+/* Applies an m x m unitary to rows `rows[0..m)` of a row-major [dim][batch] array
+ * (m <= 16).  Replaces UnitaryM.inflate + dense product for a UnitaryM with an
+ * arbitrary core (quompiler/construct/unitary.py:56-77); dim may be any size
+ * (the reference's tests use dimension 3).                                         */
+int qsv_apply_rows(qsv_ctx* ctx, void* state, uint64_t dim, uint64_t batch,
+                   const uint64_t* rows, int m, const double* matrix, void* stream);
+
+/* Programs ----------------------------------------------------------------------- */
+/* Copies a gate stream (circuit TIME order: gates[0] acts first, i.e. the order
+ * BytecodeRevIter yields, quompiler/construct/bytecode.py:69-88) and its matrix
+ * pool to the device.  QSV_ROWS2 records address rows of a [2^(n_bits-batch_bits)]
+ * [2^batch_bits] array.                                                            */
+int qsv_upload_program(qsv_ctx* ctx, int n_bits, int batch_bits, const qsv_gate_t* gates,
+                       uint64_t n_gates, const double* pool, uint64_t pool_elems);
+/* Gate-fusion pass: packs the uploaded stream into shared-memory-staged tile
+ * sweeps of at most `max_tile_bits` local bits each.  No reference counterpart
+ * (nearest analogue: the peephole SlidingWindowCombiner,
+ * quompiler/optimize/basic_optimizer.py:11-41).  Returns the number of sweeps via
+ * out_sweeps (may be NULL).                                                        */
+int qsv_fuse(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps);
+/* Runs the uploaded program on `state` (fused plan if qsv_fuse was called, else one
+ * kernel per gate).  `spare` is a second device buffer of the same size used by
+ * out-of-place (bit-permuting) sweeps, or NULL to forbid them.  On return
+ * *result_in_spare (may be NULL) is 1 if the final state lives in `spare`.
+ * Replaces functools.reduce(lambda a, b: a @ b, leaves) applied to a state
+ * (tests/qompiler/circuits/test_qompiler.py:79-82).                                 */
+int qsv_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, void* stream);
+
+/* State preparation / read-out ---------------------------------------------------- */
+/* Fills a [2^(n_bits-batch_bits)][2^batch_bits] array with basis columns: column j
+ * holds |e(col0 + j)>, where e() deposits the bits of its argument into the row-index
+ * bits NOT in ancilla_mask (ancillas start in |0>, cgate.py:289-305).  Replaces
+ * np.eye(...) (quompiler/construct/unitary.py:75).                                  */
+int qsv_init_basis_columns(qsv_ctx* ctx, void* state, int n_bits, int batch_bits,
+                           uint64_t col0, uint64_t ancilla_mask, void* stream);
+/* Gathers the rows whose ancilla bits are all 0: out is
+ * [2^(row_bits - popcount(ancilla_mask))][2^batch_bits].  Replaces CtrlGate.dela /
+ * trace / qproject with |0> (cgate.py:228-305, inter_product.py:318-363).           */
+int qsv_project_ancilla(qsv_ctx* ctx, const void* in, void* out, int n_bits, int batch_bits,
+                        uint64_t ancilla_mask, void* stream);
+/* out[y] = in[x] where bit perm[i] of y equals bit i of x.  Replaces
+ * Permuter.bitsortall + np.ix_ in CtrlGate.sorted (cgate.py:181-183,
+ * quompiler/utils/permute.py:60-121); also the local half of a qubit remap.         */
+int qsv_permute_bits(qsv_ctx* ctx, const void* in, void* out, int n_bits, const int* perm,
+                     void* stream);
+/* *out_max = max_i |a[i] - b[i]| (complex modulus) and *out_bad = number of entries
+ * with |a-b| > atol + rtol*|b|.  Synchronises `stream`.  Replaces np.allclose(v, u)
+ * (tests/qompiler/circuits/test_qompiler.py:82, quompiler/utils/mfun.py:34-52).      */
+int qsv_compare(qsv_ctx* ctx, const void* a, const void* b, uint64_t n_amps, double rtol,
+                double atol, double* out_max, uint64_t* out_bad, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QSV_H */

@@ -1,0 +1,287 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the oracle and the
+reference's golden values.  Tolerances: bit-exact for X/CNOT/MCX streams, 1e-10 max-abs for
+complex128, 1e-5 for complex64 (BASELINE.json north_star)."""
+import random
+
+import numpy as np
+import pytest
+
+import quantum_simulations_b200 as qs
+from oracle import sv_oracle as orc
+from quantum_simulations_b200 import _lib
+from quantum_simulations_b200.engine import apply_circuit, get_engine, reconstruct_unitary, reconstruct_unitary_rows
+from quantum_simulations_b200.program import flatten
+from quantum_simulations_b200.utils.mgen import (cyclic_matrix, fft_matrix, qft_circuit, random_control, random_ctrlgate,
+                                                 random_state, random_unitary)
+from tests.golden_io import STREAMS, load, unpack_gates, unpack_mats
+
+pytestmark = pytest.mark.gpu
+TOL128, TOL64 = 1e-10, 1e-5
+T, C0, C1 = qs.QType.TARGET, qs.QType.CONTROL0, qs.QType.CONTROL1
+
+
+@pytest.mark.parametrize("fuse", [False, True])
+def test_single_gate_inflate_golden(fuse):
+    d = load("single_gates")
+    for g, e in zip(unpack_gates(d), unpack_mats(d, "inflate_off", "inflate_pool")):
+        got = reconstruct_unitary([g], register=g.qspace, fuse=fuse)
+        assert np.abs(got - e).max() < TOL128
+    g = unpack_gates(d)[3]
+    assert np.abs(g.inflate() - orc.inflate_gate(g)).max() < TOL128   # the mirror's own inflate() is the GPU path
+
+
+@pytest.mark.parametrize("fuse", [False, True])
+@pytest.mark.parametrize("name", STREAMS)
+def test_stream_golden(name, fuse):
+    d = load("streams")
+    leaves = unpack_gates(d, name)
+    got = reconstruct_unitary(leaves[::-1], drop_ancilla=True, fuse=fuse)
+    want = d[f"{name}_value"]
+    assert got.shape == want.shape
+    if name in ("cfg2s", "cyc16"):
+        assert np.array_equal(got, want), "permutation stream must be bit-exact"
+    else:
+        assert np.abs(got - want).max() < TOL128
+
+
+def test_reduce_matmul_idiom_on_gpu():
+    """reduce(@).sorted().dela().inflate() -- the reference's verification idiom, unchanged."""
+    from functools import reduce
+    d = load("streams")
+    leaves = unpack_gates(d, "cfg1")
+    v = reduce(lambda a, b: a @ b, leaves)
+    got = v.sorted().dela().inflate()
+    assert np.abs(got - d["cfg1_value"]).max() < TOL128
+    assert np.allclose(got, d["cfg1_input"])
+
+
+def test_complex64_tolerance():
+    d = load("streams")
+    for name in ("cfg2c", "r4principal"):
+        leaves = unpack_gates(d, name)
+        got = reconstruct_unitary(leaves[::-1], drop_ancilla=True, dtype=np.complex64, fuse=False)
+        assert got.dtype == np.complex64
+        assert np.abs(got - d[f"{name}_value"]).max() < TOL64
+    leaves = unpack_gates(d, "cfg2s")
+    assert np.array_equal(reconstruct_unitary(leaves[::-1], drop_ancilla=True, dtype=np.complex64, fuse=False),
+                          d["cfg2s_value"].astype(np.complex64))
+
+
+@pytest.mark.parametrize("fuse", [False, True])
+def test_pairwise_products_and_dela_golden(fuse):
+    d = load("transforms")
+    for x, y, e in zip(unpack_gates(d, "mulA"), unpack_gates(d, "mulB"), unpack_mats(d, "mul_off", "mul_pool")):
+        assert np.abs((x @ y).inflate() - e).max() < TOL128
+        assert np.abs(reconstruct_unitary([y, x], fuse=fuse) - e).max() < TOL128
+    for g, e in zip(unpack_gates(d, "dela"), unpack_mats(d, "delaval_off", "delaval_pool")):
+        assert np.abs(g.dela().inflate() - e).max() < TOL128
+
+
+@pytest.mark.parametrize("fuse", [False, True])
+@pytest.mark.parametrize("n", [3, 4, 5, 6, 11, 14])
+def test_qft_matches_reference_and_fft(n, fuse):
+    circ = qft_circuit(n)
+    b = qs.get_builder(qs.QompilePlatform.B200)
+    for g in circ:
+        b.register(g.qspace)
+        b.build_gate(g)
+    circuit = b.finish()
+    if n <= 6:
+        d = load("qft")
+        u = circuit.unitary(b.all_qubits(), fuse=fuse)
+        assert np.abs(u - d[f"qft{n}_value"]).max() < TOL128
+        assert np.abs(u - fft_matrix(n)).max() < TOL128
+    x = np.stack([random_state(1 << n) for _ in range(3)], axis=1)   # ragged batch (3 -> padded to 4)
+    got = circuit.apply(x, fuse=fuse)
+    assert got.shape == x.shape
+    assert np.abs(got - orc.qft_reference(x)).max() < TOL128
+    assert np.abs(circuit.apply(x[:, 0], fuse=fuse) - orc.qft_reference(x[:, 0])).max() < TOL128
+
+
+@pytest.mark.parametrize("fuse", [False, True])
+@pytest.mark.parametrize("seed", [3, 17, 99, 12345, 777])
+def test_random_circuit_vs_oracle(seed, fuse):
+    """Random mixed circuits on 9 qubits incl. multi-target, multi-control, ancilla and diagonal gates."""
+    random.seed(seed)
+    np.random.seed(seed)
+    n = 9
+    gates = []
+    for _ in range(60):
+        k = random.randint(1, 5)
+        t = random.randint(1, min(k, 3))
+        g = random_ctrlgate(k, t, qnum=n)
+        kind = random.random()
+        if t == 1 and kind < 0.25:
+            g = qs.CtrlGate(random.choice(list(qs.UnivGate)), g.controls(), g.qspace)
+        elif t == 1 and kind < 0.4:
+            g = qs.CtrlGate(np.diag(np.exp(1j * np.random.uniform(0, 6.28, 2))), g.controls(), g.qspace)
+        gates.append(g)
+    reg = orc.register_of(gates + [qs.CtrlGate(qs.UnivGate.I, [T], [qs.Qubit(i)]) for i in range(n)])
+    x = np.stack([random_state(1 << n) for _ in range(2)], axis=1)
+    prog = flatten(gates, reg)
+    got = apply_circuit(prog, x, fuse=fuse)
+    want = orc.simulate(gates, reg, x)
+    assert np.abs(got - want).max() < TOL128
+
+
+def test_builder_conformance_template():
+    """The five checks of the reference's CircuitTestTemplate (circuit_test_template.py:21-113), with
+    the expected matrices taken from the oracle's restatement of inflate()."""
+    def run(gates, expected, register=None):
+        b = qs.get_builder(qs.QompilePlatform.B200)
+        for cu in gates:
+            b.register(cu.qspace)
+            b.build_gate(cu)
+        c = b.finish()
+        assert c is not None
+        assert np.allclose(c.unitary(b.all_qubits()), expected)
+
+    phase = qs.CtrlGate(np.array(qs.UnivGate.S), (T, C0, C1))
+    run([phase], orc.inflate_gate(phase))
+    for gate in qs.UnivGate:
+        n = random.randint(1, 4)
+        cu = qs.CtrlGate(np.array(gate), random_control(n, 1))
+        run([cu], orc.inflate_gate(cu))
+    for seed in random.sample(range(1 << 20), 10):
+        random.seed(seed)
+        np.random.seed(seed)
+        n = random.randint(1, 4)
+        k = random.randint(1, n)
+        control = random_control(n, k)
+        cu = qs.CtrlGate(random_unitary(1 << control.count(T)), control)
+        run([cu], orc.inflate_gate(cu))
+    d = load("streams")
+    leaves = unpack_gates(d, "r4ctrl_pruned")
+    run(leaves[::-1], d["r4ctrl_pruned_input"])
+
+
+def test_two_level_streams_any_dimension():
+    d = load("two_level")
+    for name, dim in (("d8", 8), ("d3", 3), ("d6", 6)):
+        us = [qs.UnitaryM(dim, tuple(c), m, p) for c, m, p in zip(d[f"{name}_core"], d[f"{name}_mat"], d[f"{name}_phase"])]
+        from functools import reduce
+        got = reduce(lambda a, b: a @ b, us).inflate()
+        assert np.abs(got - d[f"{name}_value"]).max() < TOL128
+    dim = int(d["gen_dim"])
+    off = 0
+    us = []
+    for k, core, ph in zip(d["gen_ncore"], d["gen_core"], d["gen_phase"]):
+        k = int(k)
+        us.append(qs.UnitaryM(dim, tuple(int(c) for c in core[:k]), d["gen_mat"][off:off + k * k].reshape(k, k), complex(ph)))
+        off += k * k
+    assert np.abs(reconstruct_unitary_rows(us[::-1], dim) - d["gen_value"]).max() < TOL128
+    assert np.abs(us[0].inflate() - orc.inflate_unitarym(dim, us[0].core, us[0].matrix, us[0].phase)).max() < TOL128
+    with pytest.raises(ValueError):
+        _ = (us[0] @ qs.UnitaryM(4, (0, 1), np.eye(2))).inflate()
+
+
+def test_rows2_program_records():
+    """QSV_ROWS2 records inside an uploaded program (power-of-two dimension)."""
+    from quantum_simulations_b200.program import flatten_two_level
+    d = load("two_level")
+    us = [qs.UnitaryM(8, tuple(c), m, p) for c, m, p in zip(d["d8_core"], d["d8_mat"], d["d8_phase"])]
+    prog = flatten_two_level(us[::-1], 8)
+    eng = get_engine()
+    st = eng.empty(64)
+    eng.init_basis_columns(st, 6, 3, 0, 0)
+    eng.upload_records(prog.records(), prog.pool(), 6, 3)
+    res = eng.run(st)
+    assert np.abs(res.view(8, 8).cpu().numpy() - d["d8_value"]).max() < TOL128
+
+
+def test_permute_bits_project_compare():
+    eng = get_engine()
+    import torch
+    n = 12
+    x = np.random.randn(1 << n) + 1j * np.random.randn(1 << n)
+    dx = torch.from_numpy(x).cuda()
+    perm = list(range(n))
+    random.shuffle(perm)
+    out = eng.permute_bits(dx, n, perm).cpu().numpy()
+    idx = np.arange(1 << n)
+    y = np.zeros_like(idx)
+    for i, p in enumerate(perm):
+        y |= ((idx >> i) & 1) << p
+    want = np.zeros_like(x)
+    want[y] = x
+    assert np.array_equal(out, want)
+    # project: rows with ancilla bits 0 of a [2^5][2^3] array
+    z = np.random.randn(32, 8) + 1j * np.random.randn(32, 8)
+    got = eng.project_ancilla(torch.from_numpy(z.reshape(-1)).cuda(), 8, 3, 0b01010).view(8, 8).cpu().numpy()
+    keep = [r for r in range(32) if not (r & 0b01010)]
+    assert np.array_equal(got, z[keep])
+    # fused compare
+    a = torch.from_numpy(x).cuda()
+    b2 = x.copy()
+    b2[77] += 3e-3
+    b2[900] += 1e-9
+    mx, bad = eng.compare(a, torch.from_numpy(b2).cuda(), rtol=1e-5, atol=1e-8)
+    assert abs(mx - 3e-3) < 1e-12 and bad == 1
+    assert eng.allclose(a, a) and eng.compare(a, a)[0] == 0.0
+    b2[5] = np.nan
+    assert eng.compare(a, torch.from_numpy(b2).cuda())[1] == 2
+
+
+def test_edge_cases_and_errors():
+    eng = get_engine()
+    st = eng.empty(4)
+    eng.init_basis_columns(st, 2, 1, 0, 0)
+    rec = np.zeros((), dtype=_lib.GATE_DTYPE)
+    rec["kind"], rec["n_targets"] = _lib.DENSE1, 1
+    rec["target_bits"][0] = 5                                    # out of range
+    with pytest.raises(_lib.QsvError):
+        eng.apply_gate_record(st, 2, rec, np.eye(2))
+    rec["target_bits"][0] = 1
+    rec["ctrl_mask"] = 2                                         # control == target
+    with pytest.raises(_lib.QsvError):
+        eng.apply_gate_record(st, 2, rec, np.eye(2))
+    with pytest.raises(_lib.QsvError):
+        eng.apply_rows(st, 2, 2, [0, 0], np.eye(2))              # duplicate rows
+    from quantum_simulations_b200.engine import Engine
+    fresh = Engine()
+    with pytest.raises(_lib.QsvError):
+        fresh.run(st)                                            # no program uploaded
+    fresh.close()
+    # empty program is a no-op
+    eng.upload_records(np.zeros(0, dtype=_lib.GATE_DTYPE), np.zeros(0, dtype=np.complex128), 2, 1)
+    before = st.clone()
+    eng.run(st)
+    import torch
+    assert torch.equal(before, st)
+
+
+def test_large_state_properties():
+    """Size-independent properties at a size the oracle cannot reach quickly (2^26 amplitudes):
+    unitarity (norm), QFT of a basis state = uniform magnitude, circuit followed by its inverse = identity."""
+    import torch
+    n = 26
+    eng = get_engine()
+    circ = qft_circuit(n)
+    prog = flatten(circ)
+    st = eng.empty(1 << n)
+    eng.init_basis_columns(st, n, 0, 12345, 0)
+    eng.upload(prog, 0)
+    for fuse in (False, True):
+        eng.init_basis_columns(st, n, 0, 12345, 0)
+        eng.upload(prog, 0)
+        spare = None
+        if fuse:
+            try:
+                eng.fuse()
+                spare = eng.empty(1 << n)
+            except _lib.QsvError:
+                continue
+        res = eng.run(st, spare)
+        mag = res.abs()
+        assert abs(float(torch.linalg.vector_norm(res)) - 1.0) < 1e-10
+        assert float((mag - 2.0 ** (-n / 2)).abs().max()) < 1e-12
+        # phase check on a few entries: amp[k] = exp(2 pi i k x / N) / sqrt(N)
+        ks = torch.tensor([0, 1, 2, 12345, (1 << n) - 1, 987654], device=res.device)
+        want = np.exp(2j * np.pi * ((ks.cpu().numpy().astype(object) * 12345) % (1 << n)).astype(np.float64) / (1 << n)) / 2 ** (n / 2)
+        assert np.abs(res[ks].cpu().numpy() - want).max() < 1e-10
+        # inverse circuit restores the basis state exactly enough
+        inv = [g.herm() for g in circ[::-1]]
+        eng.upload(flatten(inv), 0)
+        back = eng.run(res, None)
+        assert abs(abs(complex(back[12345])) - 1.0) < 1e-10
+        del spare
