@@ -1,0 +1,285 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: applying a compiled gate stream to a statevector on B200.
+
+Contract (see the task brief):  python bench.py --gpus N --steps K --warmup W  prints ONE JSON line.
+ * workload (N=1): QFT-30 gate circuit (30 H, 435 controlled-phase, 45 CNOT) on one complex128
+   statevector of 2^30 amplitudes (16 GiB, >> L2) -- the configuration BASELINE.json's metric names.
+   N>1: the same circuit and state sharded by the top log2(N) qubits (strong scaling), half-state
+   swaps over NCCL.  `--qubits n` selects another size (e.g. 34 on 8 GPUs).
+ * a step = one application of the whole circuit to the resident state.
+ * value = source gates / second (whole job); amp_GBps = algorithmic sweep bytes / second.
+ * e2e   = the same through host buffers: pinned H2D of the state, run, D2H of the result, every step.
+ * roofline: the dominant kernel's algorithmic bytes per launch / its CUDA-event time per launch.
+ * cpu_baseline / --impl reference: the oracle's C+OpenMP port of the reference's gate action, timed on
+   the host cores on a bounded sample (first G gates of the same circuit on the same-size state).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def qft_records(n, batch_bits=0):
+    """Flattened QFT-n circuit (time order) without building Python gate objects for every gate."""
+    from quantum_simulations_b200.utils.mgen import qft_program
+    prog = qft_program(n)
+    return prog, prog.records(batch_bits), prog.pool()
+
+
+def algorithmic_bytes(recs, n_bits, amp_bytes=16):
+    """Unfused lower bound: every gate reads+writes the amplitudes it touches."""
+    total = 0
+    for r in recs:
+        c = bin(int(r["ctrl_mask"])).count("1")
+        touched = (1 << n_bits) >> c
+        if int(r["kind"]) == 2:  # diagonal: diag(1, d) touches only target=1
+            touched >>= 1
+        total += 2 * touched * amp_bytes
+    return total
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for nm, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_sample(n, n_gates_sample):
+    """Oracle C/OpenMP port on the first `n_gates_sample` gates of QFT-n on a full-size state."""
+    from oracle import c_oracle
+    prog, recs, pool = qft_records(n)
+    g = min(n_gates_sample, len(recs))
+    st = np.full(1 << n, 2.0 ** (-n / 2), dtype=np.complex128)
+    c_oracle.run_records(recs[:1], pool, st, n)          # touch pages / warm threads
+    t0 = time.perf_counter()
+    c_oracle.run_records(recs[:g], pool, st, n)
+    dt = time.perf_counter() - t0
+    return g / dt, g, dt, c_oracle.threads()
+
+
+def run_reference(args):
+    """--impl reference: the CPU port (the reference itself is Python and cannot reach these sizes:
+    its dense-operator path needs 2^n x 2^n matrices)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n = args.qubits or 30
+    from oracle import c_oracle
+    prog, recs, pool = qft_records(n)
+    g = min(args.cpu_gates, len(recs))
+    st = np.full(1 << n, 2.0 ** (-n / 2), dtype=np.complex128)
+    for _ in range(max(1, min(args.warmup, 1))):
+        c_oracle.run_records(recs[:2], pool, st, n)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        c_oracle.run_records(recs[:g], pool, st, n)
+    dt = time.perf_counter() - t0
+    value = args.steps * g / dt
+    sample = f"first {g} of {len(recs)} QFT-{n} gates on the full 2^{n} complex128 state, per step"
+    line = {"impl": "reference", "metric": "gates_per_sec", "value": value, "unit": "gates/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "c128", "data": "synthetic",
+            "config": {"workload": f"qft{n}_statevector_c128", "qubits": n, "amplitudes": 1 << n},
+            "cpu_baseline": {"value": value, "unit": "gates/s", "cores": c_oracle.threads(), "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "gates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_single(args):
+    import torch
+    from quantum_simulations_b200.engine import Engine
+    n = args.qubits or 30
+    dev = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(dev)
+    eng = Engine(dev, np.complex128)
+    prog, recs, pool = qft_records(n)
+    n_gates = len(recs)
+    amps = 1 << n
+    state = eng.empty(amps)
+    # synthetic input: complex standard normal, L2-normalised (mgen.random_state), generated on the device
+    g = torch.Generator(device=f"cuda:{dev}")
+    g.manual_seed(42)
+    view = torch.view_as_real(state)
+    chunk = 1 << 26
+    for s in range(0, amps, chunk):
+        view[s:s + chunk].normal_(generator=g)
+    state.div_(torch.linalg.vector_norm(state))
+    eng.upload_records(recs, pool, n, 0)
+    fused = False
+    spare = None
+    n_sweeps = None
+    if not args.no_fuse:
+        try:
+            n_sweeps = eng.fuse(args.tile_bits)
+            spare = eng.empty(amps)
+            fused = True
+        except Exception as e:  # fusion pass unavailable -> per-gate kernels (still CUDA)
+            print(f"[bench] fusion unavailable: {e}", file=sys.stderr)
+    cur = state
+    other = spare
+
+    def step():
+        nonlocal cur, other
+        res = eng.run(cur, other)
+        if res is not cur:
+            cur, other = res, cur
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    eng.reset_stats()
+    sampler = ClockSampler(dev)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    st = eng.stats()
+    sec = ms / 1e3
+    value = args.steps * n_gates / sec
+    # ---- roofline of the dominant kernel ----------------------------------------------------
+    peak, peak_src = measured_peak()
+    launches = st["kernel_launches"]
+    if fused:
+        kern = "k_sweep (fused tile sweep)"
+        per_launch_bytes = 2 * amps * 16
+        prof = eng.sweep_profile() if hasattr(eng, "sweep_profile") else None
+        if prof:
+            avg_ms = float(np.mean(prof))
+        else:
+            avg_ms = ms / max(1, launches)
+        achieved = per_launch_bytes / (avg_ms * 1e-3) / 1e9
+    else:
+        kern = "k_gate1/k_phase1 (one kernel per gate; aggregate over all launches)"
+        per_launch_bytes = st["amp_bytes"] / max(1, launches)
+        avg_ms = ms / max(1, launches)
+        achieved = st["amp_bytes"] / sec / 1e9
+    amp_gbps = st["amp_bytes"] / sec / 1e9
+    # ---- e2e through host buffers -------------------------------------------------------------
+    e2e = None
+    if args.e2e_steps > 0:
+        host = torch.empty(amps, dtype=torch.complex128, pin_memory=True)
+        host.copy_(cur)
+        torch.cuda.synchronize()
+        t_e2e = []
+        for i in range(args.e2e_steps + 1):
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            cur.copy_(host, non_blocking=True)
+            res = eng.run(cur, other)
+            host.copy_(res, non_blocking=True)
+            a1.record()
+            torch.cuda.synchronize()
+            if res is not cur:
+                cur, other = res, cur
+            if i > 0:
+                t_e2e.append(a0.elapsed_time(a1))
+        e2e_ms = float(np.mean(t_e2e))
+        e2e = {"value": n_gates / (e2e_ms / 1e3), "unit": "gates/s", "h2d_bytes_per_step": amps * 16, "d2h_bytes_per_step": amps * 16,
+               "ms_per_step": e2e_ms, "steps": args.e2e_steps}
+        del host
+    # ---- CPU baseline on the host cores ---------------------------------------------------------
+    cpu = None
+    if args.cpu_gates > 0:
+        v, gcount, dt, cores = cpu_sample(n, args.cpu_gates)
+        cpu = {"value": v, "unit": "gates/s", "cores": cores, "kind": "port",
+               "sample": f"first {gcount} of {n_gates} QFT-{n} gates on the full 2^{n} complex128 state ({dt:.1f} s, C+OpenMP oracle)"}
+    line = {"metric": "gates_per_sec", "value": value, "unit": "gates/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "c128",
+            "data": "synthetic",
+            "config": {"workload": f"qft{n}_statevector_c128", "qubits": n, "amplitudes": amps, "gates": n_gates, "fused": fused,
+                       "sweeps_per_step": n_sweeps, "l2": "state (16 B x 2^n) is far larger than the 126 MB L2"},
+            "amp_GBps": amp_gbps, "hbm_frac_of_measured": amp_gbps / peak,
+            "roofline": {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                         "frac": achieved / peak, "bytes_per_launch": per_launch_bytes, "avg_launch_ms": avg_ms, "traffic": None},
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--qubits", type=int, default=0)
+    ap.add_argument("--tile-bits", type=int, default=0)
+    ap.add_argument("--no-fuse", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--cpu-gates", type=int, default=12, help="gates in the CPU baseline sample (0 = skip)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1 or args.gpus > 1:
+        from quantum_simulations_b200 import sharded
+        return sharded.bench_main(args)
+    return run_single(args)
+
+
+if __name__ == "__main__":
+    main()

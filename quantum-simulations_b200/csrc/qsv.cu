@@ -438,6 +438,14 @@ static int apply_one(qsv_ctx* ctx, void* state, int n_bits, int batch_bits, cons
     return rc;
 }
 
+// used by the fused plan for gates it cannot fuse (multi-target dense, row gates)
+int qsv_apply_planned_single(qsv_ctx* ctx, void* state, size_t gate_index, cudaStream_t s) {
+    const qsv_gate_t& g = ctx->gates[gate_index];
+    const double* h = ctx->pool.data() + 2 * g.matrix_offset;
+    const double* d = ctx->d_pool ? ctx->d_pool + 2 * g.matrix_offset : nullptr;
+    return apply_one(ctx, state, ctx->prog_bits, ctx->prog_batch_bits, &g, g.kind == QSV_PERMX ? nullptr : h, d, s);
+}
+
 extern "C" {
 
 const char* qsv_version(void) { return "qsv 0.1 (sm_100a)"; }

@@ -1,6 +1,903 @@
-// placeholder until the fused sweep lands
+// Fused tile sweep ("F" in SURVEY.md 2.1): gate-fusion pass + shared-memory-staged sweep kernel.
+//
+// One launch = one pass over the state ("sweep").  The state index is split into k LOCAL bits (the
+// tile, 2^k amplitudes staged in shared memory) and n-k GLOBAL bits (the tile id).  Every gate whose
+// target bit is local can be applied inside the tile; controls may sit anywhere (local controls are
+// tested per amplitude, global controls per tile); diagonal gates can always be applied because
+// they only need the amplitude's own index.  HBM traffic of a sweep is one read + one write of the
+// state no matter how many gates it carries.
+//
+// Inside a tile the work proceeds in REGISTER STAGES: each thread holds the 16 amplitudes that
+// differ in 4 chosen local bits (the stage's register bits), applies every op of the stage to them
+// in registers, and the tile is re-distributed through shared memory between stages (like the
+// passes of a radix-16 FFT).  Shared memory is XOR-swizzled at 16-byte granularity so that the
+// 128-bit accesses of a quarter-warp hit 8 distinct bank groups for the usual register-bit choices.
+//
+// Runs of consecutive diagonal gates with at most one control are merged on the host into a phase
+// polynomial  phi(x) = t0 + sum_a A_a x_a + sum_{a<b} B_ab x_a x_b  and applied as ONE op:
+//   register-register terms -> a 16-entry table W[j]            (uniform)
+//   register-thread terms   -> a table over the thread's bits    (host-built, read once per run)
+//   register-global terms   -> per-tile scalars (one sincos per slot per tile, kept in shared memory)
+// so a QFT sweep with 8 Hadamards and ~200 controlled phases costs 8 butterflies + 8 phase ops.
+//
+// A sweep may store the tile to a bit-permuted location of a second buffer (out of place): SWAP
+// gates then cost no arithmetic and no extra traffic.
+#include <algorithm>
+#include <cmath>
+#include <complex>
+#include <map>
+
 #include "qsv_common.cuh"
-struct SweepPlan { int dummy; };
+
+#define KMAX 12          // max local (tile) bits: 2^12 x 16 B = 64 KB of shared memory
+#define RB 4             // register bits per stage
+#define NREG 16
+#define MAX_OPS 340      // ops per launch (kernel parameter space, 32 KB limit)
+#define MAX_GSLOT 96     // per-tile phase scalars per launch
+#define MAX_SEG 12
+
+enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_DRUN = 4 };
+enum : uint8_t { FLAG_REAL = 1 };
+#define NONE16 0xFFFFu
+#define NONE32 0xFFFFFFFFu
+
+struct SwOp {  // 88 bytes
+    uint8_t type, tgt, rmask, rval;  // tgt: register bit (0..3); rmask/rval: control over the register index
+    uint16_t lmask, lval;            // control over the thread's local bits (register bits excluded)
+    uint64_t gmask, gval;            // control over the tile id
+    union {
+        double m[8];                 // OP_DENSE: 2x2 (re,im) row-major; OP_MPHASE: m[0..1] = factor
+        struct {                     // OP_STAGE
+            uint16_t roffsw[NREG];   // swizzled shared-memory slot offset of register j
+            uint8_t rpos[RB];        // local bit positions of the register bits, ascending
+            uint8_t flags;
+        } st;
+        struct {                     // OP_DRUN
+            uint32_t tbl[RB + 1];    // thread table offset (double2 units) per active bit, [RB] = c0
+            uint16_t gslot[RB + 1];  // per-tile scalar slot per active bit, [RB] = c0
+            uint32_t w_off;          // W table offset (16 double2) or NONE32
+            uint16_t wmask;          // registers j with W[j] != 1
+            uint8_t abit[RB];        // register bit index of each active slot
+            uint8_t n_active;
+        } dr;
+    };
+};
+static_assert(sizeof(SwOp) == 88, "SwOp layout");
+
+struct SegMap {  // x -> sum_s ((x >> src) & ((1<<len)-1)) << dst
+    uint8_t n, src[MAX_SEG], len[MAX_SEG], dst[MAX_SEG];
+};
+
+struct SweepDesc {
+    int n_bits, k, n_ops, n_gslots, n_glob;
+    uint32_t gcoef_off;             // doubles: per slot [1 + n_glob]
+    SegMap in_loc, out_loc, st_enum;  // local index -> physical offset (load / store), store enumeration
+    uint8_t in_glob[64], out_glob[64];  // tile-id bit -> physical bit position
+};
+
+struct SweepParams {
+    SweepDesc d;
+    SwOp ops[MAX_OPS];
+};
+static_assert(sizeof(SweepParams) < 32700, "kernel parameter space");
+
+__device__ __forceinline__ uint32_t seg_apply(uint32_t x, const SegMap& m) {
+    uint32_t r = 0;
+    for (int s = 0; s < m.n; ++s) r |= ((x >> m.src[s]) & ((1u << m.len[s]) - 1u)) << m.dst[s];
+    return r;
+}
+__device__ __forceinline__ uint64_t seg_apply64(uint32_t x, const SegMap& m) {
+    uint64_t r = 0;
+    for (int s = 0; s < m.n; ++s) r |= (uint64_t)((x >> m.src[s]) & ((1u << m.len[s]) - 1u)) << m.dst[s];
+    return r;
+}
+__host__ __device__ __forceinline__ uint32_t swz(uint32_t l) { return l ^ (((l >> 3) ^ (l >> 6) ^ (l >> 9)) & 7u); }
+
+template <typename C>
+__device__ __forceinline__ void op_dense(C (&v)[NREG], const SwOp& op, bool tpred) {
+    typedef decltype(v[0].x) R;
+    const C m00 = cmake<C, R>((R)op.m[0], (R)op.m[1]), m01 = cmake<C, R>((R)op.m[2], (R)op.m[3]);
+    const C m10 = cmake<C, R>((R)op.m[4], (R)op.m[5]), m11 = cmake<C, R>((R)op.m[6], (R)op.m[7]);
+#define BFLY(A)                                                                   \
+    _Pragma("unroll") for (int j0 = 0; j0 < NREG; ++j0) if (!(j0 & (1 << A))) {   \
+        const int j1 = j0 | (1 << A);                                             \
+        if (((j0 & op.rmask) == op.rval) && tpred) {                              \
+            const C a0 = v[j0], a1 = v[j1];                                       \
+            v[j0] = cfma(m01, a1, cmul(m00, a0));                                 \
+            v[j1] = cfma(m11, a1, cmul(m10, a0));                                 \
+        }                                                                         \
+    }
+    switch (op.tgt) {
+        case 0: BFLY(0) break;
+        case 1: BFLY(1) break;
+        case 2: BFLY(2) break;
+        default: BFLY(3) break;
+    }
+#undef BFLY
+}
+
+// real-entry matrices (H, X-like rotations about y, ...): half the multiplies
+template <typename C>
+__device__ __forceinline__ void op_dense_real(C (&v)[NREG], const SwOp& op, bool tpred) {
+    typedef decltype(v[0].x) R;
+    const R m00 = (R)op.m[0], m01 = (R)op.m[2], m10 = (R)op.m[4], m11 = (R)op.m[6];
+#define BFLYR(A)                                                                  \
+    _Pragma("unroll") for (int j0 = 0; j0 < NREG; ++j0) if (!(j0 & (1 << A))) {   \
+        const int j1 = j0 | (1 << A);                                             \
+        if (((j0 & op.rmask) == op.rval) && tpred) {                              \
+            const C a0 = v[j0], a1 = v[j1];                                       \
+            v[j0].x = fma(m01, a1.x, m00 * a0.x);                                 \
+            v[j0].y = fma(m01, a1.y, m00 * a0.y);                                 \
+            v[j1].x = fma(m11, a1.x, m10 * a0.x);                                 \
+            v[j1].y = fma(m11, a1.y, m10 * a0.y);                                 \
+        }                                                                         \
+    }
+    switch (op.tgt) {
+        case 0: BFLYR(0) break;
+        case 1: BFLYR(1) break;
+        case 2: BFLYR(2) break;
+        default: BFLYR(3) break;
+    }
+#undef BFLYR
+}
+
+template <typename C>
+__device__ __forceinline__ void op_permx(C (&v)[NREG], const SwOp& op, bool tpred) {
+#define SWP(A)                                                                    \
+    _Pragma("unroll") for (int j0 = 0; j0 < NREG; ++j0) if (!(j0 & (1 << A))) {   \
+        const int j1 = j0 | (1 << A);                                             \
+        if (((j0 & op.rmask) == op.rval) && tpred) {                              \
+            const C t = v[j0];                                                    \
+            v[j0] = v[j1];                                                        \
+            v[j1] = t;                                                            \
+        }                                                                         \
+    }
+    switch (op.tgt) {
+        case 0: SWP(0) break;
+        case 1: SWP(1) break;
+        case 2: SWP(2) break;
+        default: SWP(3) break;
+    }
+#undef SWP
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::type* __restrict__ src,
+                                                  typename cplx_of<R>::type* __restrict__ dst,
+                                                  const double* __restrict__ aux,
+                                                  const __grid_constant__ SweepParams P) {
+    typedef typename cplx_of<R>::type C;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    C* tile = reinterpret_cast<C*>(smem_raw);
+    const SweepDesc& D = P.d;
+    double2* smE = reinterpret_cast<double2*>(smem_raw + ((size_t)sizeof(C) << D.k));
+    const double2* aux2 = reinterpret_cast<const double2*>(aux);
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t tile_amps = 1u << D.k;
+    const uint32_t n_groups = tile_amps >> RB;
+    const bool active = tid < n_groups;
+    const uint64_t n_tiles = 1ull << (D.n_bits - D.k);
+
+    for (uint64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        // ---- tile base addresses and per-tile phase scalars ---------------------------------
+        uint64_t in_base = 0, out_base = 0;
+        for (int b = 0; b < D.n_glob; ++b) {
+            const uint64_t bit = (t >> b) & 1ull;
+            in_base |= bit << D.in_glob[b];
+            out_base |= bit << D.out_glob[b];
+        }
+        for (uint32_t gs = tid; gs < (uint32_t)D.n_gslots; gs += blockDim.x) {
+            const double* gc = aux + D.gcoef_off + (size_t)gs * (1 + D.n_glob);
+            double ang = gc[0];
+            for (int b = 0; b < D.n_glob; ++b)
+                if ((t >> b) & 1ull) ang += gc[1 + b];
+            double s, c;
+            sincos(ang, &s, &c);
+            smE[gs] = make_double2(c, s);
+        }
+        // ---- load the tile (coalesced 128-bit loads, swizzled shared-memory stores) ---------
+        C v[NREG];
+        // (blockDim.x * NREG == tile_amps whenever k >= 9; smaller tiles leave some slots unused)
+#pragma unroll
+        for (int i = 0; i < NREG; ++i) {
+            const uint32_t l = tid + i * blockDim.x;
+            if (l < tile_amps) v[i] = src[in_base | seg_apply64(l, D.in_loc)];
+        }
+#pragma unroll
+        for (int i = 0; i < NREG; ++i) {
+            const uint32_t l = tid + i * blockDim.x;
+            if (l < tile_amps) tile[swz(l)] = v[i];
+        }
+        __syncthreads();
+
+        uint32_t base_l = 0, swbase = 0;
+        int cur_stage = -1;
+        for (int i = 0; i < D.n_ops; ++i) {
+            const SwOp& op = P.ops[i];
+            if (op.type == OP_STAGE) {
+                if (cur_stage >= 0) {
+                    const SwOp& ps = P.ops[cur_stage];
+                    if (active) {
+#pragma unroll
+                        for (int j = 0; j < NREG; ++j) tile[swbase ^ ps.st.roffsw[j]] = v[j];
+                    }
+                    __syncthreads();
+                }
+                cur_stage = i;
+                base_l = tid;
+#pragma unroll
+                for (int q = 0; q < RB; ++q) {
+                    const uint32_t p = op.st.rpos[q];
+                    base_l = ((base_l >> p) << (p + 1)) | (base_l & ((1u << p) - 1u));
+                }
+                swbase = swz(base_l);
+                if (active) {
+#pragma unroll
+                    for (int j = 0; j < NREG; ++j) v[j] = tile[swbase ^ op.st.roffsw[j]];
+                }
+                continue;
+            }
+            if ((t & op.gmask) != op.gval) continue;  // control on a global bit not satisfied for this tile
+            if (!active) continue;
+            const bool tpred = (base_l & op.lmask) == op.lval;
+            switch (op.type) {
+                case OP_DENSE:
+                    if (op.m[1] == 0.0 && op.m[3] == 0.0 && op.m[5] == 0.0 && op.m[7] == 0.0)
+                        op_dense_real(v, op, tpred);
+                    else
+                        op_dense(v, op, tpred);
+                    break;
+                case OP_PERMX:
+                    op_permx(v, op, tpred);
+                    break;
+                case OP_MPHASE: {
+                    const C d = cmake<C, R>((R)op.m[0], (R)op.m[1]);
+#pragma unroll
+                    for (int j = 0; j < NREG; ++j)
+                        if (((j & op.rmask) == op.rval) && tpred) v[j] = cmul(v[j], d);
+                    break;
+                }
+                case OP_DRUN: {
+                    // thread-wide factor c0
+                    if (op.dr.tbl[RB] != NONE32 || op.dr.gslot[RB] != NONE16) {
+                        double2 c0 = make_double2(1.0, 0.0);
+                        if (op.dr.gslot[RB] != NONE16) c0 = smE[op.dr.gslot[RB]];
+                        if (op.dr.tbl[RB] != NONE32) c0 = cmul(c0, aux2[op.dr.tbl[RB] + tid]);
+                        const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
+#pragma unroll
+                        for (int j = 0; j < NREG; ++j) v[j] = cmul(v[j], cc);
+                    }
+                    for (int s = 0; s < op.dr.n_active; ++s) {
+                        double2 e = make_double2(1.0, 0.0);
+                        if (op.dr.gslot[s] != NONE16) e = smE[op.dr.gslot[s]];
+                        if (op.dr.tbl[s] != NONE32) e = cmul(e, aux2[op.dr.tbl[s] + tid]);
+                        const C ee = cmake<C, R>((R)e.x, (R)e.y);
+                        const int bit = 1 << op.dr.abit[s];
+#pragma unroll
+                        for (int j = 0; j < NREG; ++j)
+                            if (j & bit) v[j] = cmul(v[j], ee);
+                    }
+                    if (op.dr.w_off != NONE32) {
+#pragma unroll
+                        for (int j = 0; j < NREG; ++j)
+                            if ((op.dr.wmask >> j) & 1) {
+                                const double2 w = aux2[op.dr.w_off + j];
+                                v[j] = cmul(v[j], cmake<C, R>((R)w.x, (R)w.y));
+                            }
+                    }
+                    break;
+                }
+                default:
+                    break;
+            }
+        }
+        if (cur_stage >= 0) {
+            const SwOp& ps = P.ops[cur_stage];
+            if (active) {
+#pragma unroll
+                for (int j = 0; j < NREG; ++j) tile[swbase ^ ps.st.roffsw[j]] = v[j];
+            }
+            __syncthreads();
+        }
+        // ---- store the tile (possibly to a bit-permuted location of the other buffer) -------
+#pragma unroll
+        for (int i = 0; i < NREG; ++i) {
+            const uint32_t u = tid + i * blockDim.x;
+            if (u < tile_amps) v[i] = tile[swz(seg_apply(u, D.st_enum))];
+        }
+#pragma unroll
+        for (int i = 0; i < NREG; ++i) {
+            const uint32_t u = tid + i * blockDim.x;
+            if (u < tile_amps) dst[out_base | seg_apply64(seg_apply(u, D.st_enum), D.out_loc)] = v[i];
+        }
+        __syncthreads();
+    }
+}
+
+// ================================================================================================
+// host: fusion pass
+// ================================================================================================
+struct PlanStep {
+    bool fused;
+    size_t gate_index;      // !fused: index into ctx->gates
+    SweepParams* params;    // fused (host copy)
+    bool out_of_place;
+    uint64_t n_gates;       // source gates carried
+};
+
+struct SweepPlan {
+    std::vector<PlanStep> steps;
+    std::vector<double> aux;  // host copy of tables
+    double* d_aux = nullptr;
+    int k = 0;
+    uint64_t dropped_identities = 0;
+    std::vector<cudaEvent_t> ev;  // profiling
+    std::vector<float> ms;
+    ~SweepPlan() {
+        for (auto& s : steps) delete s.params;
+        if (d_aux) cudaFree(d_aux);
+        for (auto e : ev) cudaEventDestroy(e);
+    }
+};
+
 void sweep_plan_free(SweepPlan* p) { delete p; }
-int sweep_plan_build(qsv_ctx* ctx, int, uint64_t*) { return qsv_fail(ctx, QSV_E_UNSUPPORTED, "fusion pass not built yet"); }
-int sweep_plan_run(qsv_ctx* ctx, void*, void*, int*, cudaStream_t) { return qsv_fail(ctx, QSV_E_UNSUPPORTED, "fusion pass not built yet"); }
+
+static SegMap make_segmap(const std::vector<int>& dst_of_src) {
+    // dst_of_src[i] = destination bit of source bit i; merge consecutive runs
+    SegMap m;
+    memset(&m, 0, sizeof(m));
+    int i = 0, n = (int)dst_of_src.size();
+    while (i < n) {
+        int j = i + 1;
+        while (j < n && dst_of_src[j] == dst_of_src[j - 1] + 1) ++j;
+        m.src[m.n] = (uint8_t)i;
+        m.len[m.n] = (uint8_t)(j - i);
+        m.dst[m.n] = (uint8_t)dst_of_src[i];
+        ++m.n;
+        i = j;
+    }
+    return m;
+}
+
+namespace {
+
+struct Poly {  // phase polynomial over physical bits
+    double t0 = 0;
+    std::map<int, double> a;
+    std::map<std::pair<int, int>, double> b;
+    bool empty() const { return t0 == 0 && a.empty() && b.empty(); }
+};
+
+struct Builder {
+    qsv_ctx* ctx;
+    SweepPlan* plan;
+    int n, k, c_low;
+    // current sweep
+    std::vector<size_t> cur;  // gate indices
+    uint64_t cur_targets = 0;
+
+    Builder(qsv_ctx* c, SweepPlan* p, int n_, int k_) : ctx(c), plan(p), n(n_), k(k_) { c_low = (k < n) ? std::min(4, k - 1) : 0; }
+
+    const double* mat(const qsv_gate_t& g) const { return ctx->pool.data() + 2 * g.matrix_offset; }
+    static bool is_identity_diag(const double* m) { return m[0] == 1.0 && m[1] == 0.0 && m[6] == 1.0 && m[7] == 0.0; }
+
+    uint64_t forced_mask() const { return (1ull << c_low) - 1ull; }
+
+    bool fits(uint64_t targets) const { return __builtin_popcountll(targets | forced_mask()) <= k; }
+
+    int add_gate(size_t gi) {
+        const qsv_gate_t& g = ctx->gates[gi];
+        if (g.kind == QSV_ROWS2 || g.kind == QSV_DENSEK) {
+            int rc = flush();
+            if (rc) return rc;
+            PlanStep s{};
+            s.fused = false;
+            s.gate_index = gi;
+            s.params = nullptr;
+            s.n_gates = 1;
+            plan->steps.push_back(s);
+            return QSV_OK;
+        }
+        if (g.kind == QSV_DIAG1) {
+            if (is_identity_diag(mat(g))) {
+                plan->dropped_identities++;
+                return QSV_OK;
+            }
+            cur.push_back(gi);
+            return QSV_OK;
+        }
+        const uint64_t tb = 1ull << g.target_bits[0];
+        if (!fits(cur_targets | tb)) {
+            int rc = flush();
+            if (rc) return rc;
+        }
+        cur_targets |= tb;
+        cur.push_back(gi);
+        return QSV_OK;
+    }
+
+    // ---- emit one sweep from `cur` ----------------------------------------------------------
+    struct StageCtx {
+        std::vector<int> rloc;     // local bit positions of register bits (ascending), size RB
+        std::vector<int> tloc;     // thread local bits (ascending)
+    };
+
+    std::vector<int> tile_pos;     // physical position of each local bit
+    std::vector<int> glob_pos;     // physical position of each tile-id bit
+    int loc_of[64], glob_of[64];
+
+    void choose_tile() {
+        uint64_t m = cur_targets | forced_mask();
+        // fill with the lowest free bits (longer contiguous runs -> better coalescing)
+        for (int b = 0; b < n && __builtin_popcountll(m) < k; ++b) m |= 1ull << b;
+        tile_pos.clear();
+        glob_pos.clear();
+        for (int b = 0; b < n; ++b) {
+            loc_of[b] = glob_of[b] = -1;
+            if (m & (1ull << b)) {
+                loc_of[b] = (int)tile_pos.size();
+                tile_pos.push_back(b);
+            } else {
+                glob_of[b] = (int)glob_pos.size();
+                glob_pos.push_back(b);
+            }
+        }
+    }
+
+    // control decomposition of a (mask,value) over physical bits for the current stage
+    void split_ctrl(uint64_t mask, uint64_t value, const StageCtx& sc, SwOp& op) const {
+        op.rmask = op.rval = 0;
+        op.lmask = op.lval = 0;
+        op.gmask = op.gval = 0;
+        for (int b = 0; b < n; ++b) {
+            if (!(mask & (1ull << b))) continue;
+            const bool one = value & (1ull << b);
+            if (loc_of[b] >= 0) {
+                const int l = loc_of[b];
+                auto it = std::find(sc.rloc.begin(), sc.rloc.end(), l);
+                if (it != sc.rloc.end()) {
+                    const int ri = (int)(it - sc.rloc.begin());
+                    op.rmask |= 1u << ri;
+                    if (one) op.rval |= 1u << ri;
+                } else {
+                    op.lmask |= (uint16_t)(1u << l);
+                    if (one) op.lval |= (uint16_t)(1u << l);
+                }
+            } else {
+                op.gmask |= 1ull << glob_of[b];
+                if (one) op.gval |= 1ull << glob_of[b];
+            }
+        }
+    }
+
+    struct Emit {
+        std::vector<SwOp> ops;
+        std::vector<std::vector<double>> gslots;  // per slot: [const, coef per global bit]
+        uint64_t n_gates = 0;
+    };
+
+    int new_gslot(Emit& e, double cst, const std::vector<double>& coef) {
+        std::vector<double> s(1 + glob_pos.size(), 0.0);
+        s[0] = cst;
+        for (size_t i = 0; i < coef.size(); ++i) s[1 + i] = coef[i];
+        e.gslots.push_back(s);
+        return (int)e.gslots.size() - 1;
+    }
+
+    void emit_stage_op(Emit& e, const StageCtx& sc) {
+        SwOp op;
+        memset(&op, 0, sizeof(op));
+        op.type = OP_STAGE;
+        for (int q = 0; q < RB; ++q) op.st.rpos[q] = (uint8_t)sc.rloc[q];
+        for (int j = 0; j < NREG; ++j) {
+            uint32_t off = 0;
+            for (int q = 0; q < RB; ++q)
+                if ((j >> q) & 1) off |= 1u << sc.rloc[q];
+            op.st.roffsw[j] = (uint16_t)swz(off);
+        }
+        e.ops.push_back(op);
+    }
+
+    // close a run of diagonal gates: emit DRUN (+ MPHASE fallbacks)
+    void emit_diag_run(Emit& e, const StageCtx& sc, const std::vector<size_t>& run) {
+        if (run.empty()) return;
+        Poly P;
+        std::vector<SwOp> fallbacks;
+        auto in_reg = [&](int b) { return loc_of[b] >= 0 && std::find(sc.rloc.begin(), sc.rloc.end(), loc_of[b]) != sc.rloc.end(); };
+        for (size_t gi : run) {
+            const qsv_gate_t& g = ctx->gates[gi];
+            const double* m = mat(g);
+            const int t = g.target_bits[0];
+            const double a0 = std::atan2(m[1], m[0]), a1 = std::atan2(m[7], m[6]);
+            const int nc = __builtin_popcountll(g.ctrl_mask);
+            bool poly_ok = nc <= 1;
+            int cb = -1;
+            if (nc == 1) {
+                cb = __builtin_ctzll(g.ctrl_mask);
+                if (!in_reg(t) && !in_reg(cb)) poly_ok = false;  // a pair term needs one register bit
+            }
+            if (poly_ok) {
+                const double d = a1 - a0;
+                if (nc == 0) {
+                    P.t0 += a0;
+                    if (d != 0) P.a[t] += d;
+                } else if (g.ctrl_value & g.ctrl_mask) {  // control on 1
+                    if (a0 != 0) P.a[cb] += a0;
+                    if (d != 0) P.b[{std::min(cb, t), std::max(cb, t)}] += d;
+                } else {  // control on 0: (1 - x_c)(a0 + d x_t)
+                    P.t0 += a0;
+                    if (d != 0) P.a[t] += d;
+                    if (a0 != 0) P.a[cb] -= a0;
+                    if (d != 0) P.b[{std::min(cb, t), std::max(cb, t)}] -= d;
+                }
+            } else {
+                for (int side = 0; side < 2; ++side) {
+                    const double re = m[side ? 6 : 0], im = m[side ? 7 : 1];
+                    if (re == 1.0 && im == 0.0) continue;
+                    SwOp op;
+                    memset(&op, 0, sizeof(op));
+                    op.type = OP_MPHASE;
+                    const uint64_t tm = 1ull << t;
+                    split_ctrl(g.ctrl_mask | tm, g.ctrl_value | (side ? tm : 0), sc, op);
+                    op.m[0] = re;
+                    op.m[1] = im;
+                    fallbacks.push_back(op);
+                }
+            }
+            e.n_gates++;
+        }
+        if (!P.empty()) {
+            SwOp op;
+            memset(&op, 0, sizeof(op));
+            op.type = OP_DRUN;
+            for (int s = 0; s <= RB; ++s) {
+                op.dr.tbl[s] = NONE32;
+                op.dr.gslot[s] = NONE16;
+            }
+            op.dr.w_off = NONE32;
+            const int n_thr = (int)sc.tloc.size();
+            const size_t tbl_len = (size_t)1 << n_thr;
+            // per register bit: const, thread-bit coefs, global-bit coefs
+            double rc[RB] = {0, 0, 0, 0};
+            std::vector<std::vector<double>> rt(RB, std::vector<double>(n_thr, 0.0)), rg(RB, std::vector<double>(glob_pos.size(), 0.0));
+            double c0 = P.t0;
+            std::vector<double> ct(n_thr, 0.0), cg(glob_pos.size(), 0.0);
+            double w[RB][RB] = {{0}};
+            auto reg_index = [&](int b) -> int {
+                if (loc_of[b] < 0) return -1;
+                auto it = std::find(sc.rloc.begin(), sc.rloc.end(), loc_of[b]);
+                return it == sc.rloc.end() ? -1 : (int)(it - sc.rloc.begin());
+            };
+            auto thr_index = [&](int b) -> int {
+                if (loc_of[b] < 0) return -1;
+                auto it = std::find(sc.tloc.begin(), sc.tloc.end(), loc_of[b]);
+                return it == sc.tloc.end() ? -1 : (int)(it - sc.tloc.begin());
+            };
+            for (auto& kv : P.a) {
+                const int b = kv.first;
+                const int ri = reg_index(b);
+                if (ri >= 0) rc[ri] += kv.second;
+                else if (thr_index(b) >= 0) ct[thr_index(b)] += kv.second;
+                else cg[glob_of[b]] += kv.second;
+            }
+            for (auto& kv : P.b) {
+                const int b1 = kv.first.first, b2 = kv.first.second;
+                int r1 = reg_index(b1), r2 = reg_index(b2);
+                if (r1 >= 0 && r2 >= 0) {
+                    w[std::min(r1, r2)][std::max(r1, r2)] += kv.second;
+                } else {
+                    const int ri = r1 >= 0 ? r1 : r2;
+                    const int ob = r1 >= 0 ? b2 : b1;
+                    if (thr_index(ob) >= 0) rt[ri][thr_index(ob)] += kv.second;
+                    else rg[ri][glob_of[ob]] += kv.second;
+                }
+            }
+            auto any = [](const std::vector<double>& x) { return std::any_of(x.begin(), x.end(), [](double d) { return d != 0; }); };
+            auto make_table = [&](const std::vector<double>& coef) -> uint32_t {
+                // table over the thread id (one entry per thread group)
+                size_t off = plan->aux.size() / 2;
+                plan->aux.resize(plan->aux.size() + 2 * tbl_len);
+                for (size_t g = 0; g < tbl_len; ++g) {
+                    double ang = 0;
+                    for (int q = 0; q < n_thr; ++q)
+                        if ((g >> q) & 1) ang += coef[q];
+                    plan->aux[2 * (off + g)] = std::cos(ang);
+                    plan->aux[2 * (off + g) + 1] = std::sin(ang);
+                }
+                return (uint32_t)off;
+            };
+            // c0
+            if (any(ct)) op.dr.tbl[RB] = make_table(ct);
+            if (c0 != 0 || any(cg)) op.dr.gslot[RB] = (uint16_t)new_gslot(e, c0, cg);
+            int na = 0;
+            for (int ri = 0; ri < RB; ++ri) {
+                const bool has_t = any(rt[ri]), has_g = rc[ri] != 0 || any(rg[ri]);
+                if (!has_t && !has_g) continue;
+                op.dr.abit[na] = (uint8_t)ri;
+                if (has_t) op.dr.tbl[na] = make_table(rt[ri]);
+                if (has_g) op.dr.gslot[na] = (uint16_t)new_gslot(e, rc[ri], rg[ri]);
+                ++na;
+            }
+            op.dr.n_active = (uint8_t)na;
+            bool has_w = false;
+            for (int i = 0; i < RB; ++i)
+                for (int j = i + 1; j < RB; ++j) has_w |= w[i][j] != 0;
+            if (has_w) {
+                size_t off = plan->aux.size() / 2;
+                plan->aux.resize(plan->aux.size() + 2 * NREG);
+                uint16_t wm = 0;
+                for (int j = 0; j < NREG; ++j) {
+                    double ang = 0;
+                    for (int p = 0; p < RB; ++p)
+                        for (int q = p + 1; q < RB; ++q)
+                            if (((j >> p) & 1) && ((j >> q) & 1)) ang += w[p][q];
+                    plan->aux[2 * (off + j)] = std::cos(ang);
+                    plan->aux[2 * (off + j) + 1] = std::sin(ang);
+                    if (ang != 0) wm |= (uint16_t)(1u << j);
+                }
+                op.dr.w_off = (uint32_t)off;
+                op.dr.wmask = wm;
+            }
+            e.ops.push_back(op);
+        }
+        for (auto& f : fallbacks) e.ops.push_back(f);
+    }
+
+    void finish_stage_regs(StageCtx& sc, const std::vector<int>& want) {
+        // register bits: the wanted local bits, padded with the highest free local bits
+        std::vector<int> r = want;
+        for (int l = k - 1; l >= 0 && (int)r.size() < RB; --l)
+            if (std::find(r.begin(), r.end(), l) == r.end()) r.push_back(l);
+        std::sort(r.begin(), r.end());
+        sc.rloc = r;
+        sc.tloc.clear();
+        for (int l = 0; l < k; ++l)
+            if (std::find(r.begin(), r.end(), l) == r.end()) sc.tloc.push_back(l);
+    }
+
+    int push_sweep(Emit& e, bool out_of_place, const std::vector<int>* out_pos_of_phys) {
+        const bool has_work = std::any_of(e.ops.begin(), e.ops.end(), [](const SwOp& o) { return o.type != OP_STAGE; });
+        if (!has_work && !out_of_place) {
+            const uint64_t carried = e.n_gates;
+            e = Emit();
+            e.n_gates = carried;   // (only identities could get here)
+            return QSV_OK;
+        }
+        if (e.ops.size() > MAX_OPS || e.gslots.size() > MAX_GSLOT)
+            return qsv_fail(ctx, QSV_E_TOOBIG, "internal: sweep budget exceeded (%zu ops, %zu slots)", e.ops.size(), e.gslots.size());
+        SweepParams* sp = new SweepParams();
+        memset(sp, 0, sizeof(*sp));
+        SweepDesc& D = sp->d;
+        D.n_bits = n;
+        D.k = k;
+        D.n_ops = (int)e.ops.size();
+        D.n_gslots = (int)e.gslots.size();
+        D.n_glob = (int)glob_pos.size();
+        D.gcoef_off = (uint32_t)plan->aux.size();
+        for (auto& s : e.gslots) plan->aux.insert(plan->aux.end(), s.begin(), s.end());
+        if (plan->aux.size() & 1) plan->aux.push_back(0.0);  // keep double2 alignment
+        std::vector<int> in_dst(k), out_dst(k), enum_dst(k);
+        for (int l = 0; l < k; ++l) {
+            in_dst[l] = tile_pos[l];
+            out_dst[l] = out_pos_of_phys ? (*out_pos_of_phys)[tile_pos[l]] : tile_pos[l];
+        }
+        // store enumeration: counter bits walk the local bits in ascending OUTPUT position
+        std::vector<int> order(k);
+        for (int l = 0; l < k; ++l) order[l] = l;
+        std::sort(order.begin(), order.end(), [&](int x, int y) { return out_dst[x] < out_dst[y]; });
+        for (int u = 0; u < k; ++u) enum_dst[u] = order[u];
+        D.in_loc = make_segmap(in_dst);
+        D.out_loc = make_segmap(out_dst);
+        D.st_enum = make_segmap(enum_dst);
+        for (size_t b = 0; b < glob_pos.size(); ++b) {
+            D.in_glob[b] = (uint8_t)glob_pos[b];
+            D.out_glob[b] = (uint8_t)(out_pos_of_phys ? (*out_pos_of_phys)[glob_pos[b]] : glob_pos[b]);
+        }
+        memcpy(sp->ops, e.ops.data(), e.ops.size() * sizeof(SwOp));
+        PlanStep s{};
+        s.fused = true;
+        s.params = sp;
+        s.out_of_place = out_of_place;
+        s.n_gates = e.n_gates;
+        plan->steps.push_back(s);
+        e = Emit();
+        return QSV_OK;
+    }
+
+    int flush() {
+        if (cur.empty()) {
+            cur_targets = 0;
+            return QSV_OK;
+        }
+        choose_tile();
+        Emit e;
+        StageCtx sc;
+        std::vector<int> want;            // local bits the open stage needs in registers
+        // Two-phase per stage: first collect the gates of a stage (greedy), then emit with the final register set.
+        size_t i = 0;
+        while (i < cur.size()) {
+            // ---- collect one stage ----
+            want.clear();
+            size_t j = i;
+            for (; j < cur.size(); ++j) {
+                const qsv_gate_t& g = ctx->gates[cur[j]];
+                if (g.kind == QSV_DIAG1) continue;
+                const int l = loc_of[g.target_bits[0]];
+                if (std::find(want.begin(), want.end(), l) != want.end()) continue;
+                if ((int)want.size() == RB) break;
+                want.push_back(l);
+            }
+            // diagonal gates prefer a register bit of their own: if the stage has room, give pair gates one
+            if ((int)want.size() < RB) {
+                for (size_t q = i; q < j && (int)want.size() < RB; ++q) {
+                    const qsv_gate_t& g = ctx->gates[cur[q]];
+                    if (g.kind != QSV_DIAG1 || __builtin_popcountll(g.ctrl_mask) != 1) continue;
+                    const int t = g.target_bits[0], cb = __builtin_ctzll(g.ctrl_mask);
+                    auto has = [&](int b) { return loc_of[b] >= 0 && std::find(want.begin(), want.end(), loc_of[b]) != want.end(); };
+                    if (has(t) || has(cb)) continue;
+                    if (loc_of[t] >= 0) want.push_back(loc_of[t]);
+                    else if (loc_of[cb] >= 0) want.push_back(loc_of[cb]);
+                }
+            }
+            finish_stage_regs(sc, want);
+            // budgets: a launch carries at most MAX_OPS ops and MAX_GSLOT per-tile scalars; when either
+            // would overflow, the sweep is closed and the same stage is reopened in the next launch
+            auto ensure = [&](size_t ops_needed, size_t slots_needed) -> int {
+                if (e.ops.size() + ops_needed > MAX_OPS || e.gslots.size() + slots_needed > MAX_GSLOT) {
+                    int rc = push_sweep(e, false, nullptr);
+                    if (rc) return rc;
+                    emit_stage_op(e, sc);
+                }
+                return QSV_OK;
+            };
+            if (e.ops.size() + 16 > MAX_OPS || e.gslots.size() + 2 * (RB + 1) > MAX_GSLOT) {
+                int rc = push_sweep(e, false, nullptr);
+                if (rc) return rc;
+            }
+            emit_stage_op(e, sc);
+            std::vector<size_t> run;
+            const size_t RUN_CHUNK = 64;
+            for (size_t q = i; q < j; ++q) {
+                const qsv_gate_t& g = ctx->gates[cur[q]];
+                if (g.kind == QSV_DIAG1) {
+                    run.push_back(cur[q]);
+                    if (run.size() >= RUN_CHUNK) {
+                        int rc = ensure(2 * RUN_CHUNK + 2, RB + 1);
+                        if (rc) return rc;
+                        emit_diag_run(e, sc, run);
+                        run.clear();
+                    }
+                    continue;
+                }
+                int rc = ensure(2 * run.size() + 3, RB + 1);
+                if (rc) return rc;
+                emit_diag_run(e, sc, run);
+                run.clear();
+                SwOp op;
+                memset(&op, 0, sizeof(op));
+                op.type = g.kind == QSV_PERMX ? OP_PERMX : OP_DENSE;
+                const int l = loc_of[g.target_bits[0]];
+                const uint8_t tg = (uint8_t)(std::find(sc.rloc.begin(), sc.rloc.end(), l) - sc.rloc.begin());
+                split_ctrl(g.ctrl_mask, g.ctrl_value, sc, op);
+                op.tgt = tg;
+                if (g.kind != QSV_PERMX) memcpy(op.m, mat(g), 8 * sizeof(double));
+                e.ops.push_back(op);
+                e.n_gates++;
+            }
+            {
+                int rc = ensure(2 * run.size() + 2, RB + 1);
+                if (rc) return rc;
+                emit_diag_run(e, sc, run);
+                run.clear();
+            }
+            i = j;
+        }
+        int rc = push_sweep(e, false, nullptr);
+        cur.clear();
+        cur_targets = 0;
+        return rc;
+    }
+};
+
+}  // namespace
+
+int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
+    const int n = ctx->prog_bits;
+    if (n < RB) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "unsupported: fused sweeps need at least %d index bits (have %d)", RB, n);
+    int k = max_tile_bits > 0 ? max_tile_bits : KMAX;
+    k = std::min(std::min(k, KMAX), n);
+    if (k < RB) return qsv_fail(ctx, QSV_E_INVALID, "max_tile_bits must be >= %d", RB);
+    if (ctx->plan) {
+        sweep_plan_free(ctx->plan);
+        ctx->plan = nullptr;
+    }
+    SweepPlan* plan = new SweepPlan();
+    plan->k = k;
+    plan->aux.resize(2, 0.0);  // offset 0 reserved
+    Builder b(ctx, plan, n, k);
+    for (size_t i = 0; i < ctx->gates.size(); ++i) {
+        int rc = b.add_gate(i);
+        if (rc) {
+            delete plan;
+            return rc;
+        }
+    }
+    int rc = b.flush();
+    if (rc) {
+        delete plan;
+        return rc;
+    }
+    cudaError_t e = cudaMalloc(&plan->d_aux, plan->aux.size() * sizeof(double));
+    if (e == cudaSuccess) e = cudaMemcpy(plan->d_aux, plan->aux.data(), plan->aux.size() * sizeof(double), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        delete plan;
+        return qsv_fail(ctx, QSV_E_CUDA, "uploading the sweep tables failed: %s", cudaGetErrorString(e));
+    }
+    // opt in to > 48 KB of dynamic shared memory
+    const int smem = (int)((amp_size(ctx->dtype) << k) + MAX_GSLOT * sizeof(double2));
+    if (ctx->dtype == QSV_C128)
+        e = cudaFuncSetAttribute(k_sweep<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    else
+        e = cudaFuncSetAttribute(k_sweep<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+        delete plan;
+        return qsv_fail(ctx, QSV_E_CUDA, "cudaFuncSetAttribute(%d B smem) failed: %s", smem, cudaGetErrorString(e));
+    }
+    ctx->plan = plan;
+    if (out_sweeps) {
+        uint64_t s = 0;
+        for (auto& st : plan->steps) s += st.fused;
+        *out_sweeps = s;
+    }
+    return QSV_OK;
+}
+
+// defined in qsv.cu
+int qsv_apply_planned_single(qsv_ctx* ctx, void* state, size_t gate_index, cudaStream_t s);
+
+int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream) {
+    SweepPlan* plan = ctx->plan;
+    const int n = ctx->prog_bits, k = plan->k;
+    void* cur = state;
+    void* other = spare;
+    int sm_count = 148;
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
+    const size_t smem = (amp_size(ctx->dtype) << k) + MAX_GSLOT * sizeof(double2);
+    const int threads = std::max(32, 1 << (k - RB));
+    const uint64_t n_tiles = 1ull << (n - k);
+    int occ = 1;
+    if (ctx->dtype == QSV_C128)
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<double>, threads, smem);
+    else
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<float>, threads, smem);
+    occ = std::max(occ, 1);
+    const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)sm_count * occ);
+    for (auto& st : plan->steps) {
+        if (!st.fused) {
+            int rc = qsv_apply_planned_single(ctx, cur, st.gate_index, stream);
+            if (rc) return rc;
+            continue;
+        }
+        void* dstp = cur;
+        if (st.out_of_place) {
+            if (!other) return qsv_fail(ctx, QSV_E_INVALID, "this plan has bit-permuting sweeps: pass a spare buffer to qsv_run");
+            dstp = other;
+        }
+        if (ctx->dtype == QSV_C128)
+            k_sweep<double><<<grid, threads, smem, stream>>>((const double2*)cur, (double2*)dstp, plan->d_aux, *st.params);
+        else
+            k_sweep<float><<<grid, threads, smem, stream>>>((const float2*)cur, (float2*)dstp, plan->d_aux, *st.params);
+        QSV_CUDA(ctx, cudaGetLastError());
+        ctx->stats.kernel_launches++;
+        ctx->stats.sweeps++;
+        ctx->stats.fused_sweeps++;
+        ctx->stats.amp_bytes += 2 * (amp_size(ctx->dtype) << n);
+        ctx->stats.gates_applied += st.n_gates;
+        if (st.out_of_place) std::swap(cur, other);
+    }
+    ctx->stats.gates_applied += plan->dropped_identities;
+    if (result_in_spare) *result_in_spare = (cur != state);
+    else if (cur != state) return qsv_fail(ctx, QSV_E_INVALID, "result landed in the spare buffer but result_in_spare is NULL");
+    return QSV_OK;
+}

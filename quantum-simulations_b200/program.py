@@ -101,6 +101,22 @@ class Program:
             rec["matrix_offset"] = self._push_matrix(m)
         self._recs.append(rec)
 
+    def add_raw(self, target_bits, ctrl_mask, ctrl_value, matrix):
+        """Append a gate given directly by register bit positions (no CtrlGate object, hence none of
+        its tolerance-based snapping to named gates, cgate.py:33-37)."""
+        m = np.asarray(matrix, dtype=np.complex128)
+        t = len(target_bits)
+        assert m.shape == (1 << t, 1 << t) and 1 <= t <= MAX_TARGETS
+        rec = np.zeros((), dtype=GATE_DTYPE)
+        rec["n_targets"] = t
+        rec["target_bits"][:t] = list(target_bits)
+        rec["ctrl_mask"] = ctrl_mask
+        rec["ctrl_value"] = ctrl_value
+        kind = classify_1q(m) if t == 1 else DENSEK
+        rec["kind"] = kind
+        rec["matrix_offset"] = 0 if kind == PERMX else self._push_matrix(m)
+        self._recs.append(rec)
+
     def add_two_level(self, u):
         """Append a UnitaryM with a 2-index core (unitary.py:26-46) as a row gate."""
         assert len(u.core) == 2

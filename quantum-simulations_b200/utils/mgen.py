@@ -91,3 +91,29 @@ def qft_circuit(n: int):
         gates.append(CtrlGate(UnivGate.X, [T, C1], [a, b]))
         gates.append(CtrlGate(UnivGate.X, [C1, T], [a, b]))
     return gates
+
+
+def qft_program(n: int):
+    """The same QFT-n circuit as :func:`qft_circuit`, flattened directly with EXACT phases.
+
+    Going through ``CtrlGate`` snaps any matrix within ``np.allclose`` tolerance of a named gate to
+    that gate (reference behaviour, cgate.py:33-37), which turns the controlled phases with
+    angle < ~1e-5 (j - i >= 19) into identities; benchmarks and large-n FFT checks want the exact
+    transform, so they use this generator.
+    """
+    from ..program import Program
+    prog = Program([Qubit(i) for i in range(n)])
+    h = np.array(UnivGate.H)
+    x = np.array(UnivGate.X)
+    bit = lambda i: n - 1 - i
+    for i in range(n):
+        prog.add_raw([bit(i)], 0, 0, h)
+        for j in range(i + 1, n):
+            ph = np.exp(2j * np.pi / (1 << (j - i + 1)))
+            prog.add_raw([bit(i)], 1 << bit(j), 1 << bit(j), np.array([[1, 0], [0, ph]]))
+    for i in range(n // 2):
+        a, b = bit(i), bit(n - 1 - i)
+        prog.add_raw([b], 1 << a, 1 << a, x)
+        prog.add_raw([a], 1 << b, 1 << b, x)
+        prog.add_raw([b], 1 << a, 1 << a, x)
+    return prog

@@ -92,7 +92,12 @@ def test_qft_matches_reference_and_fft(n, fuse):
         assert np.abs(u - d[f"qft{n}_value"]).max() < TOL128
         assert np.abs(u - fft_matrix(n)).max() < TOL128
     x = np.stack([random_state(1 << n) for _ in range(3)], axis=1)   # ragged batch (3 -> padded to 4)
+    eng = get_engine()
+    eng.reset_stats()
     got = circuit.apply(x, fuse=fuse)
+    st = eng.stats()
+    assert (st["fused_sweeps"] > 0) == fuse, st          # the fused kernel really ran (or really did not)
+    assert st["gates_applied"] == len(circ)
     assert got.shape == x.shape
     assert np.abs(got - orc.qft_reference(x)).max() < TOL128
     assert np.abs(circuit.apply(x[:, 0], fuse=fuse) - orc.qft_reference(x[:, 0])).max() < TOL128
@@ -256,11 +261,9 @@ def test_large_state_properties():
     import torch
     n = 26
     eng = get_engine()
-    circ = qft_circuit(n)
-    prog = flatten(circ)
+    from quantum_simulations_b200.utils.mgen import qft_program
+    prog = qft_program(n)          # exact phases (CtrlGate would snap angles < 1e-5 to identity, as the reference does)
     st = eng.empty(1 << n)
-    eng.init_basis_columns(st, n, 0, 12345, 0)
-    eng.upload(prog, 0)
     for fuse in (False, True):
         eng.init_basis_columns(st, n, 0, 12345, 0)
         eng.upload(prog, 0)
@@ -279,9 +282,12 @@ def test_large_state_properties():
         ks = torch.tensor([0, 1, 2, 12345, (1 << n) - 1, 987654], device=res.device)
         want = np.exp(2j * np.pi * ((ks.cpu().numpy().astype(object) * 12345) % (1 << n)).astype(np.float64) / (1 << n)) / 2 ** (n / 2)
         assert np.abs(res[ks].cpu().numpy() - want).max() < 1e-10
-        # inverse circuit restores the basis state exactly enough
-        inv = [g.herm() for g in circ[::-1]]
-        eng.upload(flatten(inv), 0)
-        back = eng.run(res, None)
-        assert abs(abs(complex(back[12345])) - 1.0) < 1e-10
+        # linearity / unitarity: QFT of the uniform superposition of all basis states is |0>
+        res.fill_(2.0 ** (-n / 2))
+        eng.upload(prog, 0)
+        if fuse:
+            eng.fuse()
+        back = eng.run(res, spare if spare is not None else None)
+        assert abs(complex(back[0]) - 1.0) < 1e-10
+        assert float(back[1:].abs().max()) < 1e-10
         del spare
