@@ -27,9 +27,22 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 
+CIRCUIT = "qft"
+
+
 def qft_records(n, batch_bits=0):
-    """Flattened QFT-n circuit (time order) without building Python gate objects for every gate."""
+    """Flattened QFT-n circuit (time order) without building Python gate objects for every gate.
+    Diagnostic circuits: --circuit hlayer:LO:HI = Hadamards on bits LO..HI-1 (one sweep each tile set)."""
     from quantum_simulations_b200.utils.mgen import qft_program
+    if CIRCUIT.startswith("hlayer"):
+        from quantum_simulations_b200.construct.qspace import Qubit
+        from quantum_simulations_b200.construct.types import UnivGate
+        from quantum_simulations_b200.program import Program
+        _, lo, hi = CIRCUIT.split(":")
+        prog = Program([Qubit(i) for i in range(n)])
+        for b in range(int(lo), int(hi)):
+            prog.add_raw([b], 0, 0, np.array(UnivGate.H))
+        return prog, prog.records(batch_bits), prog.pool()
     prog = qft_program(n)
     return prog, prog.records(batch_bits), prog.pool()
 
@@ -187,6 +200,8 @@ def run_single(args):
         step()
     torch.cuda.synchronize()
     eng.reset_stats()
+    if fused:
+        eng.set_profiling(True)
     sampler = ClockSampler(dev)
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -207,13 +222,13 @@ def run_single(args):
     if fused:
         kern = "k_sweep (fused tile sweep)"
         per_launch_bytes = 2 * amps * 16
-        prof = eng.sweep_profile() if hasattr(eng, "sweep_profile") else None
-        if prof:
-            avg_ms = float(np.mean(prof))
-        else:
-            avg_ms = ms / max(1, launches)
+        prof = eng.sweep_profile()
+        eng.set_profiling(False)
+        sweep_ms = [round(x, 3) for x in prof[:n_sweeps]] if prof else None
+        avg_ms = float(np.mean(prof)) if prof else ms / max(1, launches)
         achieved = per_launch_bytes / (avg_ms * 1e-3) / 1e9
     else:
+        sweep_ms = None
         kern = "k_gate1/k_phase1 (one kernel per gate; aggregate over all launches)"
         per_launch_bytes = st["amp_bytes"] / max(1, launches)
         avg_ms = ms / max(1, launches)
@@ -256,7 +271,7 @@ def run_single(args):
             "amp_GBps": amp_gbps, "hbm_frac_of_measured": amp_gbps / peak,
             "roofline": {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": achieved / peak, "bytes_per_launch": per_launch_bytes, "avg_launch_ms": avg_ms, "traffic": None},
-            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "sweep_ms_first_step": sweep_ms}
     print(json.dumps(line))
 
 
@@ -271,7 +286,10 @@ def main():
     ap.add_argument("--no-fuse", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-gates", type=int, default=12, help="gates in the CPU baseline sample (0 = skip)")
+    ap.add_argument("--circuit", default="qft", help="qft | hlayer:LO:HI (diagnostic)")
     args = ap.parse_args()
+    global CIRCUIT
+    CIRCUIT = args.circuit
     if args.impl == "reference":
         return run_reference(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))

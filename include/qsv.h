@@ -134,6 +134,13 @@ int qsv_fuse(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps);
  * (tests/qompiler/circuits/test_qompiler.py:79-82).                                 */
 int qsv_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, void* stream);
 
+/* Profiling: when on, every fused sweep launched by qsv_run is bracketed by CUDA events on the
+ * launch stream; qsv_get_sweep_profile waits for them and returns their durations in launch
+ * order (*n_out = how many were recorded, at most `cap` are written).  No reference
+ * counterpart (the reference has no timers on this path).                                */
+int qsv_set_profiling(qsv_ctx* ctx, int on);
+int qsv_get_sweep_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out);
+
 /* State preparation / read-out ---------------------------------------------------- */
 /* Fills a [2^(n_bits-batch_bits)][2^batch_bits] array with basis columns: column j
  * holds |e(col0 + j)>, where e() deposits the bits of its argument into the row-index

@@ -608,6 +608,18 @@ int qsv_fuse(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
     return sweep_plan_build(ctx, max_tile_bits, out_sweeps);
 }
 
+int qsv_set_profiling(qsv_ctx* ctx, int on) {
+    if (!ctx) return QSV_E_INVALID;
+    ctx->profile = on != 0;
+    return QSV_OK;
+}
+
+int qsv_get_sweep_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out) {
+    if (!ctx) return QSV_E_INVALID;
+    QSV_CUDA(ctx, cudaSetDevice(ctx->device));
+    return sweep_plan_collect_profile(ctx, ms, cap, n_out);
+}
+
 int qsv_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, void* stream) {
     if (!ctx) return QSV_E_INVALID;
     if (!ctx->has_program) return qsv_fail(ctx, QSV_E_NOPROGRAM, "qsv_run before qsv_upload_program");

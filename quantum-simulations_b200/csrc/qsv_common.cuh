@@ -75,6 +75,7 @@ struct qsv_ctx {
     double* d_pool = nullptr;      // device copy
     // fused plan
     SweepPlan* plan = nullptr;
+    bool profile = false;          // record CUDA events around every fused sweep
 };
 
 int qsv_fail(qsv_ctx* ctx, int code, const char* fmt, ...);
@@ -92,3 +93,4 @@ static inline size_t amp_size(int dtype) { return dtype == QSV_C128 ? 16 : 8; }
 void sweep_plan_free(SweepPlan* p);
 int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps);
 int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream);
+int sweep_plan_collect_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out);

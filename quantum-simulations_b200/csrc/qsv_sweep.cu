@@ -69,10 +69,15 @@ struct SegMap {  // x -> sum_s ((x >> src) & ((1<<len)-1)) << dst
 };
 
 struct SweepDesc {
-    int n_bits, k, n_ops, n_gslots, n_glob;
+    int n_bits, k, n_ops, n_gslots, n_glob, tb;  // tb = log2(blockDim)
     uint32_t gcoef_off;             // doubles: per slot [1 + n_glob]
     SegMap in_loc, out_loc, st_enum;  // local index -> physical offset (load / store), store enumeration
     uint8_t in_glob[64], out_glob[64];  // tile-id bit -> physical bit position
+    // All index maps are bitwise-linear, so the tile copy splits every address into a per-thread part
+    // (computed once per kernel from the maps above) and a per-slot part (below, host-computed):
+    // slot i of thread tid handles local index  tid | (i << tb)  on load and  st_enum(tid | (i << tb))  on store.
+    uint64_t ld_goff[NREG], st_goff[NREG];  // global offset contributed by slot i
+    uint16_t ld_soff[NREG], st_soff[NREG];  // swizzled shared-memory slot contributed by slot i
 };
 
 struct SweepParams {
@@ -178,6 +183,14 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
     const uint32_t n_groups = tile_amps >> RB;
     const bool active = tid < n_groups;
     const uint64_t n_tiles = 1ull << (D.n_bits - D.k);
+    // amplitudes each thread copies (<= NREG); tiles smaller than a warp use only the first tile_amps threads
+    const int n_slots = (tid < tile_amps) ? (int)max(1u, tile_amps >> D.tb) : 0;
+    // per-thread parts of the tile-copy addresses (tile independent)
+    const uint64_t t_ld_g = seg_apply64(tid, D.in_loc);
+    const uint32_t t_ld_s = swz(tid);
+    const uint32_t t_st_l = seg_apply(tid, D.st_enum);
+    const uint64_t t_st_g = seg_apply64(t_st_l, D.out_loc);
+    const uint32_t t_st_s = swz(t_st_l);
 
     for (uint64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
         // ---- tile base addresses and per-tile phase scalars ---------------------------------
@@ -199,15 +212,14 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
         // ---- load the tile (coalesced 128-bit loads, swizzled shared-memory stores) ---------
         C v[NREG];
         // (blockDim.x * NREG == tile_amps whenever k >= 9; smaller tiles leave some slots unused)
+        {
+            const uint64_t gb = in_base | t_ld_g;
 #pragma unroll
-        for (int i = 0; i < NREG; ++i) {
-            const uint32_t l = tid + i * blockDim.x;
-            if (l < tile_amps) v[i] = src[in_base | seg_apply64(l, D.in_loc)];
-        }
+            for (int i = 0; i < NREG; ++i)
+                if (i < n_slots) v[i] = src[gb | D.ld_goff[i]];
 #pragma unroll
-        for (int i = 0; i < NREG; ++i) {
-            const uint32_t l = tid + i * blockDim.x;
-            if (l < tile_amps) tile[swz(l)] = v[i];
+            for (int i = 0; i < NREG; ++i)
+                if (i < n_slots) tile[t_ld_s ^ D.ld_soff[i]] = v[i];
         }
         __syncthreads();
 
@@ -301,15 +313,14 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
             __syncthreads();
         }
         // ---- store the tile (possibly to a bit-permuted location of the other buffer) -------
+        {
+            const uint64_t gb = out_base | t_st_g;
 #pragma unroll
-        for (int i = 0; i < NREG; ++i) {
-            const uint32_t u = tid + i * blockDim.x;
-            if (u < tile_amps) v[i] = tile[swz(seg_apply(u, D.st_enum))];
-        }
+            for (int i = 0; i < NREG; ++i)
+                if (i < n_slots) v[i] = tile[t_st_s ^ D.st_soff[i]];
 #pragma unroll
-        for (int i = 0; i < NREG; ++i) {
-            const uint32_t u = tid + i * blockDim.x;
-            if (u < tile_amps) dst[out_base | seg_apply64(seg_apply(u, D.st_enum), D.out_loc)] = v[i];
+            for (int i = 0; i < NREG; ++i)
+                if (i < n_slots) dst[gb | D.st_goff[i]] = v[i];
         }
         __syncthreads();
     }
@@ -690,6 +701,24 @@ struct Builder {
         D.in_loc = make_segmap(in_dst);
         D.out_loc = make_segmap(out_dst);
         D.st_enum = make_segmap(enum_dst);
+        D.tb = std::max(5, k - RB);
+        for (int i = 0; i < NREG; ++i) {
+            const uint32_t l_ld = (uint32_t)i << D.tb;
+            if (l_ld >= (1u << k)) break;
+            uint32_t l_st = 0;
+            uint64_t g_ld = 0, g_st = 0;
+            for (int b = 0; b < k; ++b)
+                if ((l_ld >> b) & 1) {
+                    g_ld |= 1ull << in_dst[b];
+                    l_st |= 1u << enum_dst[b];
+                }
+            for (int b = 0; b < k; ++b)
+                if ((l_st >> b) & 1) g_st |= 1ull << out_dst[b];
+            D.ld_goff[i] = g_ld;
+            D.ld_soff[i] = (uint16_t)swz(l_ld);
+            D.st_goff[i] = g_st;
+            D.st_soff[i] = (uint16_t)swz(l_st);
+        }
         for (size_t b = 0; b < glob_pos.size(); ++b) {
             D.in_glob[b] = (uint8_t)glob_pos[b];
             D.out_glob[b] = (uint8_t)(out_pos_of_phys ? (*out_pos_of_phys)[glob_pos[b]] : glob_pos[b]);
@@ -884,11 +913,22 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
             if (!other) return qsv_fail(ctx, QSV_E_INVALID, "this plan has bit-permuting sweeps: pass a spare buffer to qsv_run");
             dstp = other;
         }
+        cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+        if (ctx->profile) {
+            QSV_CUDA(ctx, cudaEventCreate(&ev0));
+            QSV_CUDA(ctx, cudaEventCreate(&ev1));
+            QSV_CUDA(ctx, cudaEventRecord(ev0, stream));
+        }
         if (ctx->dtype == QSV_C128)
             k_sweep<double><<<grid, threads, smem, stream>>>((const double2*)cur, (double2*)dstp, plan->d_aux, *st.params);
         else
             k_sweep<float><<<grid, threads, smem, stream>>>((const float2*)cur, (float2*)dstp, plan->d_aux, *st.params);
         QSV_CUDA(ctx, cudaGetLastError());
+        if (ctx->profile) {
+            QSV_CUDA(ctx, cudaEventRecord(ev1, stream));
+            plan->ev.push_back(ev0);
+            plan->ev.push_back(ev1);
+        }
         ctx->stats.kernel_launches++;
         ctx->stats.sweeps++;
         ctx->stats.fused_sweeps++;
@@ -899,5 +939,25 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
     ctx->stats.gates_applied += plan->dropped_identities;
     if (result_in_spare) *result_in_spare = (cur != state);
     else if (cur != state) return qsv_fail(ctx, QSV_E_INVALID, "result landed in the spare buffer but result_in_spare is NULL");
+    return QSV_OK;
+}
+
+// Collects the CUDA-event durations of the fused sweeps launched since the last call (profiling mode).
+int sweep_plan_collect_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out) {
+    SweepPlan* plan = ctx->plan;
+    int n = 0;
+    if (plan) {
+        for (size_t i = 0; i + 1 < plan->ev.size(); i += 2) {
+            QSV_CUDA(ctx, cudaEventSynchronize(plan->ev[i + 1]));
+            float t = 0;
+            QSV_CUDA(ctx, cudaEventElapsedTime(&t, plan->ev[i], plan->ev[i + 1]));
+            if (n < cap && ms) ms[n] = t;
+            ++n;
+            cudaEventDestroy(plan->ev[i]);
+            cudaEventDestroy(plan->ev[i + 1]);
+        }
+        plan->ev.clear();
+    }
+    if (n_out) *n_out = n;
     return QSV_OK;
 }

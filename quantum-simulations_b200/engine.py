@@ -110,6 +110,16 @@ class Engine:
         check(self.lib.qsv_run(self._ctx, C.c_void_p(state.data_ptr()), sp, C.byref(flag), self._stream()), self._ctx)
         return spare if flag.value else state
 
+    def set_profiling(self, on: bool):
+        check(self.lib.qsv_set_profiling(self._ctx, int(bool(on))), self._ctx)
+
+    def sweep_profile(self, cap: int = 4096):
+        """CUDA-event durations (ms) of the fused sweeps launched since the last call."""
+        buf = (C.c_float * cap)()
+        n = C.c_int(0)
+        check(self.lib.qsv_get_sweep_profile(self._ctx, buf, cap, C.byref(n)), self._ctx)
+        return [float(buf[i]) for i in range(min(cap, n.value))]
+
     # -- single operations -----------------------------------------------------------
     def apply_gate_record(self, state, n_bits: int, rec, matrix):
         rec = np.ascontiguousarray(rec, dtype=_lib.GATE_DTYPE)
