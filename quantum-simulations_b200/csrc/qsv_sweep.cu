@@ -15,13 +15,16 @@
 //
 // Runs of consecutive diagonal gates with at most one control are merged on the host into a phase
 // polynomial  phi(x) = t0 + sum_a A_a x_a + sum_{a<b} B_ab x_a x_b  and applied as ONE op:
-//   register-register terms -> a 16-entry table W[j]            (uniform)
-//   register-thread terms   -> a table over the thread's bits    (host-built, read once per run)
+//   register-register terms -> a 16-entry table W[j]                              (shared memory)
+//   register-thread terms   -> two 16-entry tables over 4-bit chunks of the thread id (shared memory,
+//                              copied once per CTA), multiplied together
 //   register-global terms   -> per-tile scalars (one sincos per slot per tile, kept in shared memory)
 // so a QFT sweep with 8 Hadamards and ~200 controlled phases costs 8 butterflies + 8 phase ops.
 //
 // A sweep may store the tile to a bit-permuted location of a second buffer (out of place): SWAP
 // gates then cost no arithmetic and no extra traffic.
+#include <stdlib.h>
+
 #include <algorithm>
 #include <cmath>
 #include <complex>
@@ -34,6 +37,8 @@
 #define NREG 16
 #define MAX_OPS 340      // ops per launch (kernel parameter space, 32 KB limit)
 #define MAX_GSLOT 96     // per-tile phase scalars per launch
+#define MAX_TAB 1024     // double2 entries of phase tables per launch (16 KB of shared memory)
+#define TSLOT_LEN 32     // one thread-phase slot = 2 chunks x 16 entries
 #define MAX_SEG 12
 
 enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_DRUN = 4 };
@@ -53,9 +58,9 @@ struct SwOp {  // 88 bytes
             uint8_t flags;
         } st;
         struct {                     // OP_DRUN
-            uint32_t tbl[RB + 1];    // thread table offset (double2 units) per active bit, [RB] = c0
+            uint16_t tslot[RB + 1];  // thread-phase slot (offset into the shared tables) per active bit, [RB] = c0
             uint16_t gslot[RB + 1];  // per-tile scalar slot per active bit, [RB] = c0
-            uint32_t w_off;          // W table offset (16 double2) or NONE32
+            uint16_t w_off;          // W table offset (16 entries) or NONE16
             uint16_t wmask;          // registers j with W[j] != 1
             uint8_t abit[RB];        // register bit index of each active slot
             uint8_t n_active;
@@ -78,6 +83,12 @@ struct SweepDesc {
     // slot i of thread tid handles local index  tid | (i << tb)  on load and  st_enum(tid | (i << tb))  on store.
     uint64_t ld_goff[NREG], st_goff[NREG];  // global offset contributed by slot i
     uint16_t ld_soff[NREG], st_soff[NREG];  // swizzled shared-memory slot contributed by slot i
+    // When the first (last) stage keeps only high local bits in registers, the tile is loaded
+    // (stored) straight into (from) that stage's register layout and skips one trip through
+    // shared memory: slot j is then register j and the thread part is the stage's base index.
+    uint8_t direct_load, direct_store;
+    uint8_t first_rpos[RB], last_rpos[RB];
+    uint32_t tab_off, tab_len;              // shared phase tables: aux offset / length in double2 units
 };
 
 struct SweepParams {
@@ -98,7 +109,7 @@ __device__ __forceinline__ uint64_t seg_apply64(uint32_t x, const SegMap& m) {
 }
 __host__ __device__ __forceinline__ uint32_t swz(uint32_t l) { return l ^ (((l >> 3) ^ (l >> 6) ^ (l >> 9)) & 7u); }
 
-template <typename C>
+template <typename C, bool CTRL>
 __device__ __forceinline__ void op_dense(C (&v)[NREG], const SwOp& op, bool tpred) {
     typedef decltype(v[0].x) R;
     const C m00 = cmake<C, R>((R)op.m[0], (R)op.m[1]), m01 = cmake<C, R>((R)op.m[2], (R)op.m[3]);
@@ -106,7 +117,7 @@ __device__ __forceinline__ void op_dense(C (&v)[NREG], const SwOp& op, bool tpre
 #define BFLY(A)                                                                   \
     _Pragma("unroll") for (int j0 = 0; j0 < NREG; ++j0) if (!(j0 & (1 << A))) {   \
         const int j1 = j0 | (1 << A);                                             \
-        if (((j0 & op.rmask) == op.rval) && tpred) {                              \
+        if (!CTRL || (((j0 & op.rmask) == op.rval) && tpred)) {                   \
             const C a0 = v[j0], a1 = v[j1];                                       \
             v[j0] = cfma(m01, a1, cmul(m00, a0));                                 \
             v[j1] = cfma(m11, a1, cmul(m10, a0));                                 \
@@ -121,15 +132,15 @@ __device__ __forceinline__ void op_dense(C (&v)[NREG], const SwOp& op, bool tpre
 #undef BFLY
 }
 
-// real-entry matrices (H, X-like rotations about y, ...): half the multiplies
-template <typename C>
+// real-entry matrices (H, rotations about y, ...): half the multiplies
+template <typename C, bool CTRL>
 __device__ __forceinline__ void op_dense_real(C (&v)[NREG], const SwOp& op, bool tpred) {
     typedef decltype(v[0].x) R;
     const R m00 = (R)op.m[0], m01 = (R)op.m[2], m10 = (R)op.m[4], m11 = (R)op.m[6];
 #define BFLYR(A)                                                                  \
     _Pragma("unroll") for (int j0 = 0; j0 < NREG; ++j0) if (!(j0 & (1 << A))) {   \
         const int j1 = j0 | (1 << A);                                             \
-        if (((j0 & op.rmask) == op.rval) && tpred) {                              \
+        if (!CTRL || (((j0 & op.rmask) == op.rval) && tpred)) {                   \
             const C a0 = v[j0], a1 = v[j1];                                       \
             v[j0].x = fma(m01, a1.x, m00 * a0.x);                                 \
             v[j0].y = fma(m01, a1.y, m00 * a0.y);                                 \
@@ -166,6 +177,15 @@ __device__ __forceinline__ void op_permx(C (&v)[NREG], const SwOp& op, bool tpre
 #undef SWP
 }
 
+__device__ __forceinline__ uint32_t expand_rb(uint32_t g, const uint8_t* rpos) {
+#pragma unroll
+    for (int q = 0; q < RB; ++q) {
+        const uint32_t p = rpos[q];
+        g = ((g >> p) << (p + 1)) | (g & ((1u << p) - 1u));
+    }
+    return g;
+}
+
 template <typename R>
 __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::type* __restrict__ src,
                                                   typename cplx_of<R>::type* __restrict__ dst,
@@ -176,6 +196,7 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
     C* tile = reinterpret_cast<C*>(smem_raw);
     const SweepDesc& D = P.d;
     double2* smE = reinterpret_cast<double2*>(smem_raw + ((size_t)sizeof(C) << D.k));
+    double2* smT = smE + MAX_GSLOT;
     const double2* aux2 = reinterpret_cast<const double2*>(aux);
 
     const uint32_t tid = threadIdx.x;
@@ -183,40 +204,46 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
     const uint32_t n_groups = tile_amps >> RB;
     const bool active = tid < n_groups;
     const uint64_t n_tiles = 1ull << (D.n_bits - D.k);
-    // amplitudes each thread copies (<= NREG); tiles smaller than a warp use only the first tile_amps threads
-    const int n_slots = (tid < tile_amps) ? (int)max(1u, tile_amps >> D.tb) : 0;
     // per-thread parts of the tile-copy addresses (tile independent)
-    const uint64_t t_ld_g = seg_apply64(tid, D.in_loc);
-    const uint32_t t_ld_s = swz(tid);
-    const uint32_t t_st_l = seg_apply(tid, D.st_enum);
+    const bool dload = D.direct_load, dstore = D.direct_store;
+    const uint32_t t_ld_l = dload ? expand_rb(tid, D.first_rpos) : tid;
+    const uint64_t t_ld_g = seg_apply64(t_ld_l, D.in_loc);
+    const uint32_t t_ld_s = swz(t_ld_l);
+    const uint32_t t_st_l = dstore ? expand_rb(tid, D.last_rpos) : seg_apply(tid, D.st_enum);
     const uint64_t t_st_g = seg_apply64(t_st_l, D.out_loc);
     const uint32_t t_st_s = swz(t_st_l);
+    // amplitudes each thread copies (<= NREG); tiles smaller than a warp use only the first tile_amps threads
+    const int n_slots = (tid < tile_amps) ? (int)max(1u, tile_amps >> D.tb) : 0;
+
+    // phase tables of this sweep: global -> shared, once per CTA
+    for (uint32_t i = tid; i < D.tab_len; i += blockDim.x) smT[i] = aux2[D.tab_off + i];
 
     for (uint64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        // ---- tile base addresses and per-tile phase scalars ---------------------------------
+        // ---- tile base addresses ---------------------------------------------------------------
         uint64_t in_base = 0, out_base = 0;
         for (int b = 0; b < D.n_glob; ++b) {
             const uint64_t bit = (t >> b) & 1ull;
             in_base |= bit << D.in_glob[b];
             out_base |= bit << D.out_glob[b];
         }
-        for (uint32_t gs = tid; gs < (uint32_t)D.n_gslots; gs += blockDim.x) {
-            const double* gc = aux + D.gcoef_off + (size_t)gs * (1 + D.n_glob);
-            double ang = gc[0];
-            for (int b = 0; b < D.n_glob; ++b)
-                if ((t >> b) & 1ull) ang += gc[1 + b];
-            double s, c;
-            sincos(ang, &s, &c);
-            smE[gs] = make_double2(c, s);
-        }
-        // ---- load the tile (coalesced 128-bit loads, swizzled shared-memory stores) ---------
+        // ---- issue the tile loads first (coalesced 128-bit), then do the per-tile scalars --------
         C v[NREG];
-        // (blockDim.x * NREG == tile_amps whenever k >= 9; smaller tiles leave some slots unused)
         {
             const uint64_t gb = in_base | t_ld_g;
 #pragma unroll
             for (int i = 0; i < NREG; ++i)
                 if (i < n_slots) v[i] = src[gb | D.ld_goff[i]];
+        }
+        for (uint32_t gs = tid; gs < (uint32_t)D.n_gslots; gs += blockDim.x) {
+            const double* gc = aux + D.gcoef_off + (size_t)gs * (1 + D.n_glob);
+            double ang = gc[0];
+            for (int b = 0; b < D.n_glob; ++b)
+                if ((t >> b) & 1ull) ang += gc[1 + b];
+            double sn, cs;
+            sincos(ang, &sn, &cs);
+            smE[gs] = make_double2(cs, sn);
+        }
+        if (!dload) {
 #pragma unroll
             for (int i = 0; i < NREG; ++i)
                 if (i < n_slots) tile[t_ld_s ^ D.ld_soff[i]] = v[i];
@@ -225,6 +252,7 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
 
         uint32_t base_l = 0, swbase = 0;
         int cur_stage = -1;
+        bool regs_loaded = dload;
         for (int i = 0; i < D.n_ops; ++i) {
             const SwOp& op = P.ops[i];
             if (op.type == OP_STAGE) {
@@ -237,14 +265,11 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
                     __syncthreads();
                 }
                 cur_stage = i;
-                base_l = tid;
-#pragma unroll
-                for (int q = 0; q < RB; ++q) {
-                    const uint32_t p = op.st.rpos[q];
-                    base_l = ((base_l >> p) << (p + 1)) | (base_l & ((1u << p) - 1u));
-                }
+                base_l = expand_rb(tid, op.st.rpos);
                 swbase = swz(base_l);
-                if (active) {
+                if (regs_loaded) {
+                    regs_loaded = false;  // the direct load already put this stage's amplitudes in v[]
+                } else if (active) {
 #pragma unroll
                     for (int j = 0; j < NREG; ++j) v[j] = tile[swbase ^ op.st.roffsw[j]];
                 }
@@ -253,13 +278,19 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
             if ((t & op.gmask) != op.gval) continue;  // control on a global bit not satisfied for this tile
             if (!active) continue;
             const bool tpred = (base_l & op.lmask) == op.lval;
+            const bool ctrl = (op.rmask | op.lmask) != 0;
             switch (op.type) {
-                case OP_DENSE:
-                    if (op.m[1] == 0.0 && op.m[3] == 0.0 && op.m[5] == 0.0 && op.m[7] == 0.0)
-                        op_dense_real(v, op, tpred);
-                    else
-                        op_dense(v, op, tpred);
+                case OP_DENSE: {
+                    const bool real = op.m[1] == 0.0 && op.m[3] == 0.0 && op.m[5] == 0.0 && op.m[7] == 0.0;
+                    if (real) {
+                        if (ctrl) op_dense_real<C, true>(v, op, tpred);
+                        else op_dense_real<C, false>(v, op, true);
+                    } else {
+                        if (ctrl) op_dense<C, true>(v, op, tpred);
+                        else op_dense<C, false>(v, op, true);
+                    }
                     break;
+                }
                 case OP_PERMX:
                     op_permx(v, op, tpred);
                     break;
@@ -271,11 +302,12 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
                     break;
                 }
                 case OP_DRUN: {
+                    const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
                     // thread-wide factor c0
-                    if (op.dr.tbl[RB] != NONE32 || op.dr.gslot[RB] != NONE16) {
+                    if (op.dr.tslot[RB] != NONE16 || op.dr.gslot[RB] != NONE16) {
                         double2 c0 = make_double2(1.0, 0.0);
                         if (op.dr.gslot[RB] != NONE16) c0 = smE[op.dr.gslot[RB]];
-                        if (op.dr.tbl[RB] != NONE32) c0 = cmul(c0, aux2[op.dr.tbl[RB] + tid]);
+                        if (op.dr.tslot[RB] != NONE16) c0 = cmul(c0, cmul(smT[op.dr.tslot[RB] + c_lo], smT[op.dr.tslot[RB] + c_hi]));
                         const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
 #pragma unroll
                         for (int j = 0; j < NREG; ++j) v[j] = cmul(v[j], cc);
@@ -283,18 +315,18 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
                     for (int s = 0; s < op.dr.n_active; ++s) {
                         double2 e = make_double2(1.0, 0.0);
                         if (op.dr.gslot[s] != NONE16) e = smE[op.dr.gslot[s]];
-                        if (op.dr.tbl[s] != NONE32) e = cmul(e, aux2[op.dr.tbl[s] + tid]);
+                        if (op.dr.tslot[s] != NONE16) e = cmul(e, cmul(smT[op.dr.tslot[s] + c_lo], smT[op.dr.tslot[s] + c_hi]));
                         const C ee = cmake<C, R>((R)e.x, (R)e.y);
                         const int bit = 1 << op.dr.abit[s];
 #pragma unroll
                         for (int j = 0; j < NREG; ++j)
                             if (j & bit) v[j] = cmul(v[j], ee);
                     }
-                    if (op.dr.w_off != NONE32) {
+                    if (op.dr.w_off != NONE16) {
 #pragma unroll
                         for (int j = 0; j < NREG; ++j)
                             if ((op.dr.wmask >> j) & 1) {
-                                const double2 w = aux2[op.dr.w_off + j];
+                                const double2 w = smT[op.dr.w_off + j];
                                 v[j] = cmul(v[j], cmake<C, R>((R)w.x, (R)w.y));
                             }
                     }
@@ -304,16 +336,22 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
                     break;
             }
         }
-        if (cur_stage >= 0) {
-            const SwOp& ps = P.ops[cur_stage];
+        // ---- store the tile (possibly to a bit-permuted location of the other buffer) ----------
+        if (dstore && cur_stage >= 0) {
+            const uint64_t gb = out_base | t_st_g;
             if (active) {
 #pragma unroll
-                for (int j = 0; j < NREG; ++j) tile[swbase ^ ps.st.roffsw[j]] = v[j];
+                for (int j = 0; j < NREG; ++j) dst[gb | D.st_goff[j]] = v[j];
             }
-            __syncthreads();
-        }
-        // ---- store the tile (possibly to a bit-permuted location of the other buffer) -------
-        {
+        } else {
+            if (cur_stage >= 0) {
+                const SwOp& ps = P.ops[cur_stage];
+                if (active) {
+#pragma unroll
+                    for (int j = 0; j < NREG; ++j) tile[swbase ^ ps.st.roffsw[j]] = v[j];
+                }
+                __syncthreads();
+            }
             const uint64_t gb = out_base | t_st_g;
 #pragma unroll
             for (int i = 0; i < NREG; ++i)
@@ -322,7 +360,7 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
             for (int i = 0; i < NREG; ++i)
                 if (i < n_slots) dst[gb | D.st_goff[i]] = v[i];
         }
-        __syncthreads();
+        __syncthreads();  // shared memory (tile, per-tile scalars) is rewritten by the next tile
     }
 }
 
@@ -485,6 +523,8 @@ struct Builder {
     struct Emit {
         std::vector<SwOp> ops;
         std::vector<std::vector<double>> gslots;  // per slot: [const, coef per global bit]
+        std::vector<double> tab;                  // shared phase tables of this launch (re,im pairs)
+        std::vector<int> first_rloc, last_rloc;   // register bits of the first / last stage
         uint64_t n_gates = 0;
     };
 
@@ -507,6 +547,8 @@ struct Builder {
                 if ((j >> q) & 1) off |= 1u << sc.rloc[q];
             op.st.roffsw[j] = (uint16_t)swz(off);
         }
+        if (e.first_rloc.empty()) e.first_rloc = sc.rloc;
+        e.last_rloc = sc.rloc;
         e.ops.push_back(op);
     }
 
@@ -563,12 +605,11 @@ struct Builder {
             memset(&op, 0, sizeof(op));
             op.type = OP_DRUN;
             for (int s = 0; s <= RB; ++s) {
-                op.dr.tbl[s] = NONE32;
+                op.dr.tslot[s] = NONE16;
                 op.dr.gslot[s] = NONE16;
             }
-            op.dr.w_off = NONE32;
+            op.dr.w_off = NONE16;
             const int n_thr = (int)sc.tloc.size();
-            const size_t tbl_len = (size_t)1 << n_thr;
             // per register bit: const, thread-bit coefs, global-bit coefs
             double rc[RB] = {0, 0, 0, 0};
             std::vector<std::vector<double>> rt(RB, std::vector<double>(n_thr, 0.0)), rg(RB, std::vector<double>(glob_pos.size(), 0.0));
@@ -605,28 +646,31 @@ struct Builder {
                 }
             }
             auto any = [](const std::vector<double>& x) { return std::any_of(x.begin(), x.end(), [](double d) { return d != 0; }); };
-            auto make_table = [&](const std::vector<double>& coef) -> uint32_t {
-                // table over the thread id (one entry per thread group)
-                size_t off = plan->aux.size() / 2;
-                plan->aux.resize(plan->aux.size() + 2 * tbl_len);
-                for (size_t g = 0; g < tbl_len; ++g) {
-                    double ang = 0;
-                    for (int q = 0; q < n_thr; ++q)
-                        if ((g >> q) & 1) ang += coef[q];
-                    plan->aux[2 * (off + g)] = std::cos(ang);
-                    plan->aux[2 * (off + g) + 1] = std::sin(ang);
-                }
-                return (uint32_t)off;
+            auto make_table = [&](const std::vector<double>& coef) -> uint16_t {
+            // two 16-entry tables over the low / high 4-bit chunk of the thread id
+                const size_t off = e.tab.size() / 2;
+                e.tab.resize(e.tab.size() + 2 * TSLOT_LEN);
+                for (int chunk = 0; chunk < 2; ++chunk)
+                    for (int vv = 0; vv < 16; ++vv) {
+                        double ang = 0;
+                        for (int q = 0; q < 4; ++q) {
+                            const int tb_i = chunk * 4 + q;
+                            if (tb_i < n_thr && ((vv >> q) & 1)) ang += coef[tb_i];
+                        }
+                        e.tab[2 * (off + chunk * 16 + vv)] = std::cos(ang);
+                        e.tab[2 * (off + chunk * 16 + vv) + 1] = std::sin(ang);
+                    }
+                return (uint16_t)off;
             };
             // c0
-            if (any(ct)) op.dr.tbl[RB] = make_table(ct);
+            if (any(ct)) op.dr.tslot[RB] = make_table(ct);
             if (c0 != 0 || any(cg)) op.dr.gslot[RB] = (uint16_t)new_gslot(e, c0, cg);
             int na = 0;
             for (int ri = 0; ri < RB; ++ri) {
                 const bool has_t = any(rt[ri]), has_g = rc[ri] != 0 || any(rg[ri]);
                 if (!has_t && !has_g) continue;
                 op.dr.abit[na] = (uint8_t)ri;
-                if (has_t) op.dr.tbl[na] = make_table(rt[ri]);
+                if (has_t) op.dr.tslot[na] = make_table(rt[ri]);
                 if (has_g) op.dr.gslot[na] = (uint16_t)new_gslot(e, rc[ri], rg[ri]);
                 ++na;
             }
@@ -635,19 +679,19 @@ struct Builder {
             for (int i = 0; i < RB; ++i)
                 for (int j = i + 1; j < RB; ++j) has_w |= w[i][j] != 0;
             if (has_w) {
-                size_t off = plan->aux.size() / 2;
-                plan->aux.resize(plan->aux.size() + 2 * NREG);
+                const size_t off = e.tab.size() / 2;
+                e.tab.resize(e.tab.size() + 2 * NREG);
                 uint16_t wm = 0;
                 for (int j = 0; j < NREG; ++j) {
                     double ang = 0;
                     for (int p = 0; p < RB; ++p)
                         for (int q = p + 1; q < RB; ++q)
                             if (((j >> p) & 1) && ((j >> q) & 1)) ang += w[p][q];
-                    plan->aux[2 * (off + j)] = std::cos(ang);
-                    plan->aux[2 * (off + j) + 1] = std::sin(ang);
+                    e.tab[2 * (off + j)] = std::cos(ang);
+                    e.tab[2 * (off + j) + 1] = std::sin(ang);
                     if (ang != 0) wm |= (uint16_t)(1u << j);
                 }
-                op.dr.w_off = (uint32_t)off;
+                op.dr.w_off = (uint16_t)off;
                 op.dr.wmask = wm;
             }
             e.ops.push_back(op);
@@ -675,8 +719,9 @@ struct Builder {
             e.n_gates = carried;   // (only identities could get here)
             return QSV_OK;
         }
-        if (e.ops.size() > MAX_OPS || e.gslots.size() > MAX_GSLOT)
-            return qsv_fail(ctx, QSV_E_TOOBIG, "internal: sweep budget exceeded (%zu ops, %zu slots)", e.ops.size(), e.gslots.size());
+        if (e.ops.size() > MAX_OPS || e.gslots.size() > MAX_GSLOT || e.tab.size() / 2 > MAX_TAB)
+            return qsv_fail(ctx, QSV_E_TOOBIG, "internal: sweep budget exceeded (%zu ops, %zu slots, %zu table entries)", e.ops.size(),
+                            e.gslots.size(), e.tab.size() / 2);
         SweepParams* sp = new SweepParams();
         memset(sp, 0, sizeof(*sp));
         SweepDesc& D = sp->d;
@@ -688,6 +733,9 @@ struct Builder {
         D.gcoef_off = (uint32_t)plan->aux.size();
         for (auto& s : e.gslots) plan->aux.insert(plan->aux.end(), s.begin(), s.end());
         if (plan->aux.size() & 1) plan->aux.push_back(0.0);  // keep double2 alignment
+        D.tab_off = (uint32_t)(plan->aux.size() / 2);
+        D.tab_len = (uint32_t)(e.tab.size() / 2);
+        plan->aux.insert(plan->aux.end(), e.tab.begin(), e.tab.end());
         std::vector<int> in_dst(k), out_dst(k), enum_dst(k);
         for (int l = 0; l < k; ++l) {
             in_dst[l] = tile_pos[l];
@@ -702,21 +750,50 @@ struct Builder {
         D.out_loc = make_segmap(out_dst);
         D.st_enum = make_segmap(enum_dst);
         D.tb = std::max(5, k - RB);
+        // direct global <-> register paths: need full tiles (k >= 9) and a stage whose register bits
+        // leave the lowest local bits to the lanes, so that the accesses stay coalesced
+        auto high_only = [](const std::vector<int>& r) { return !r.empty() && r[0] >= 4; };
+        static const bool no_direct = getenv("QSV_NO_DIRECT") != nullptr;  // debugging aid
+        D.direct_load = !no_direct && has_work && k >= 9 && high_only(e.first_rloc);
+        D.direct_store = !no_direct && has_work && k >= 9 && !out_of_place && high_only(e.last_rloc);
+        for (int q = 0; q < RB; ++q) {
+            D.first_rpos[q] = (uint8_t)(e.first_rloc.empty() ? q : e.first_rloc[q]);
+            D.last_rpos[q] = (uint8_t)(e.last_rloc.empty() ? q : e.last_rloc[q]);
+        }
+        auto dep = [&](uint32_t l, const std::vector<int>& dstpos) {
+            uint64_t g = 0;
+            for (int b = 0; b < k; ++b)
+                if ((l >> b) & 1) g |= 1ull << dstpos[b];
+            return g;
+        };
         for (int i = 0; i < NREG; ++i) {
-            const uint32_t l_ld = (uint32_t)i << D.tb;
-            if (l_ld >= (1u << k)) break;
-            uint32_t l_st = 0;
-            uint64_t g_ld = 0, g_st = 0;
-            for (int b = 0; b < k; ++b)
-                if ((l_ld >> b) & 1) {
-                    g_ld |= 1ull << in_dst[b];
-                    l_st |= 1u << enum_dst[b];
-                }
-            for (int b = 0; b < k; ++b)
-                if ((l_st >> b) & 1) g_st |= 1ull << out_dst[b];
-            D.ld_goff[i] = g_ld;
-            D.ld_soff[i] = (uint16_t)swz(l_ld);
-            D.st_goff[i] = g_st;
+            // load side
+            uint32_t l_ld;
+            if (D.direct_load) {
+                l_ld = 0;
+                for (int q = 0; q < RB; ++q)
+                    if ((i >> q) & 1) l_ld |= 1u << e.first_rloc[q];
+            } else {
+                l_ld = (uint32_t)i << D.tb;
+            }
+            if (l_ld < (1u << k)) {
+                D.ld_goff[i] = dep(l_ld, in_dst);
+                D.ld_soff[i] = (uint16_t)swz(l_ld);
+            }
+            // store side
+            uint32_t l_st;
+            if (D.direct_store) {
+                l_st = 0;
+                for (int q = 0; q < RB; ++q)
+                    if ((i >> q) & 1) l_st |= 1u << e.last_rloc[q];
+            } else {
+                const uint32_t u = (uint32_t)i << D.tb;
+                if (u >= (1u << k)) continue;
+                l_st = 0;
+                for (int b = 0; b < k; ++b)
+                    if ((u >> b) & 1) l_st |= 1u << enum_dst[b];
+            }
+            D.st_goff[i] = dep(l_st, out_dst);
             D.st_soff[i] = (uint16_t)swz(l_st);
         }
         for (size_t b = 0; b < glob_pos.size(); ++b) {
@@ -772,15 +849,17 @@ struct Builder {
             finish_stage_regs(sc, want);
             // budgets: a launch carries at most MAX_OPS ops and MAX_GSLOT per-tile scalars; when either
             // would overflow, the sweep is closed and the same stage is reopened in the next launch
+            const size_t TAB_PER_RUN = (RB + 1) * TSLOT_LEN + NREG;
             auto ensure = [&](size_t ops_needed, size_t slots_needed) -> int {
-                if (e.ops.size() + ops_needed > MAX_OPS || e.gslots.size() + slots_needed > MAX_GSLOT) {
+                if (e.ops.size() + ops_needed > MAX_OPS || e.gslots.size() + slots_needed > MAX_GSLOT ||
+                    e.tab.size() / 2 + TAB_PER_RUN > MAX_TAB) {
                     int rc = push_sweep(e, false, nullptr);
                     if (rc) return rc;
                     emit_stage_op(e, sc);
                 }
                 return QSV_OK;
             };
-            if (e.ops.size() + 16 > MAX_OPS || e.gslots.size() + 2 * (RB + 1) > MAX_GSLOT) {
+            if (e.ops.size() + 16 > MAX_OPS || e.gslots.size() + 2 * (RB + 1) > MAX_GSLOT || e.tab.size() / 2 + 2 * TAB_PER_RUN > MAX_TAB) {
                 int rc = push_sweep(e, false, nullptr);
                 if (rc) return rc;
             }
@@ -835,6 +914,7 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
     const int n = ctx->prog_bits;
     if (n < RB) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "unsupported: fused sweeps need at least %d index bits (have %d)", RB, n);
     int k = max_tile_bits > 0 ? max_tile_bits : KMAX;
+    if (max_tile_bits <= 0 && getenv("QSV_TILE_BITS")) k = atoi(getenv("QSV_TILE_BITS"));  // tuning / debugging aid
     k = std::min(std::min(k, KMAX), n);
     if (k < RB) return qsv_fail(ctx, QSV_E_INVALID, "max_tile_bits must be >= %d", RB);
     if (ctx->plan) {
@@ -864,7 +944,7 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
         return qsv_fail(ctx, QSV_E_CUDA, "uploading the sweep tables failed: %s", cudaGetErrorString(e));
     }
     // opt in to > 48 KB of dynamic shared memory
-    const int smem = (int)((amp_size(ctx->dtype) << k) + MAX_GSLOT * sizeof(double2));
+    const int smem = (int)((amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2));
     if (ctx->dtype == QSV_C128)
         e = cudaFuncSetAttribute(k_sweep<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     else
@@ -892,7 +972,7 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
     void* other = spare;
     int sm_count = 148;
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
-    const size_t smem = (amp_size(ctx->dtype) << k) + MAX_GSLOT * sizeof(double2);
+    const size_t smem = (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2);
     const int threads = std::max(32, 1 << (k - RB));
     const uint64_t n_tiles = 1ull << (n - k);
     int occ = 1;
@@ -924,6 +1004,8 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
         else
             k_sweep<float><<<grid, threads, smem, stream>>>((const float2*)cur, (float2*)dstp, plan->d_aux, *st.params);
         QSV_CUDA(ctx, cudaGetLastError());
+        static const bool sync_each = getenv("QSV_SYNC") != nullptr;  // debugging aid: surface kernel faults at the launch site
+        if (sync_each) QSV_CUDA(ctx, cudaStreamSynchronize(stream));
         if (ctx->profile) {
             QSV_CUDA(ctx, cudaEventRecord(ev1, stream));
             plan->ev.push_back(ev0);
