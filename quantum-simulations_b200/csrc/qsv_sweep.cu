@@ -35,18 +35,32 @@
 #define KMAX 12          // max local (tile) bits: 2^12 x 16 B = 64 KB of shared memory
 #define RB 4             // register bits per stage
 #define NREG 16
-#define MAX_OPS 340      // ops per launch (kernel parameter space, 32 KB limit)
+#define MAX_OPS 320      // ops per launch (kernel parameter space, 32 KB limit)
 #define MAX_GSLOT 96     // per-tile phase scalars per launch
 #define MAX_TAB 1024     // double2 entries of phase tables per launch (16 KB of shared memory)
 #define TSLOT_LEN 32     // one thread-phase slot = 2 chunks x 16 entries
 #define MAX_SEG 12
 
-enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_DRUN = 4 };
+enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_DRUN = 4, OP_DRUN1 = 5 };
+// Dispatch codes (SwOp::type as stored): the host resolves op kind, target register bit, real/complex
+// and controlled/uncontrolled into ONE small integer so that the device decodes an op with a single
+// jump-table branch.
+enum : uint8_t {
+    DC_STAGE = 0,
+    DC_DENSE_REAL_NC = 1,    // +tgt (4 codes each)
+    DC_DENSE_CPLX_NC = 5,
+    DC_DENSE_REAL_C = 9,
+    DC_DENSE_CPLX_C = 13,
+    DC_PERMX = 17,
+    DC_DRUN1 = 21,           // +active register bit
+    DC_MPHASE = 25,
+    DC_DRUN = 26,
+};
 enum : uint8_t { FLAG_REAL = 1 };
 #define NONE16 0xFFFFu
 #define NONE32 0xFFFFFFFFu
 
-struct SwOp {  // 88 bytes
+struct __align__(16) SwOp {  // 96 bytes = 6 x 16 B, fetched one op ahead into registers
     uint8_t type, tgt, rmask, rval;  // tgt: register bit (0..3); rmask/rval: control over the register index
     uint16_t lmask, lval;            // control over the thread's local bits (register bits excluded)
     uint64_t gmask, gval;            // control over the tile id
@@ -67,17 +81,22 @@ struct SwOp {  // 88 bytes
         } dr;
     };
 };
-static_assert(sizeof(SwOp) == 88, "SwOp layout");
+static_assert(sizeof(SwOp) == 96, "SwOp layout");
 
 struct SegMap {  // x -> sum_s ((x >> src) & ((1<<len)-1)) << dst
     uint8_t n, src[MAX_SEG], len[MAX_SEG], dst[MAX_SEG];
 };
 
+struct SegMap64 {  // same over up to 64 source bits (tile id -> global offset)
+    uint8_t n, src[48], len[48], dst[48];
+};
+
 struct SweepDesc {
     int n_bits, k, n_ops, n_gslots, n_glob, tb;  // tb = log2(blockDim)
-    uint32_t gcoef_off;             // doubles: per slot [1 + n_glob]
+    uint32_t gtab_off;              // double2 units: per per-tile scalar slot, g_chunks x 16 entries
+    int g_chunks;                   // ceil(n_glob / 4), at least 1
     SegMap in_loc, out_loc, st_enum;  // local index -> physical offset (load / store), store enumeration
-    uint8_t in_glob[64], out_glob[64];  // tile-id bit -> physical bit position
+    SegMap64 in_glob, out_glob;     // tile id -> physical base offset (load / store)
     // All index maps are bitwise-linear, so the tile copy splits every address into a per-thread part
     // (computed once per kernel from the maps above) and a per-slot part (below, host-computed):
     // slot i of thread tid handles local index  tid | (i << tb)  on load and  st_enum(tid | (i << tb))  on store.
@@ -107,74 +126,98 @@ __device__ __forceinline__ uint64_t seg_apply64(uint32_t x, const SegMap& m) {
     for (int s = 0; s < m.n; ++s) r |= (uint64_t)((x >> m.src[s]) & ((1u << m.len[s]) - 1u)) << m.dst[s];
     return r;
 }
+__device__ __forceinline__ uint64_t seg_apply64x(uint64_t x, const SegMap64& m) {
+    uint64_t r = 0;
+    for (int s = 0; s < m.n; ++s) r |= ((x >> m.src[s]) & ((1ull << m.len[s]) - 1ull)) << m.dst[s];
+    return r;
+}
 __host__ __device__ __forceinline__ uint32_t swz(uint32_t l) { return l ^ (((l >> 3) ^ (l >> 6) ^ (l >> 9)) & 7u); }
 
-template <typename C, bool CTRL>
-__device__ __forceinline__ void op_dense(C (&v)[NREG], const SwOp& op, bool tpred) {
+// An op held in registers: header words + 64-byte payload (all accesses statically indexed).
+struct OpR {
+    uint32_t w0, w1;       // w0 = type | tgt<<8 | rmask<<16 | rval<<24 ; w1 = lmask | lval<<16
+    uint64_t gmask, gval;
+    uint64_t p[8];         // payload: matrix doubles / stage table / run slots
+    __device__ __forceinline__ uint32_t type() const { return w0 & 0xFFu; }
+    __device__ __forceinline__ uint32_t tgt() const { return (w0 >> 8) & 0xFFu; }
+    __device__ __forceinline__ uint32_t rmask() const { return (w0 >> 16) & 0xFFu; }
+    __device__ __forceinline__ uint32_t rval() const { return w0 >> 24; }
+    __device__ __forceinline__ uint32_t lmask() const { return w1 & 0xFFFFu; }
+    __device__ __forceinline__ uint32_t lval() const { return w1 >> 16; }
+    __device__ __forceinline__ double m(int i) const { return __longlong_as_double((long long)p[i]); }
+    // OP_STAGE payload: roffsw[16] (u16) then rpos[4] (u8)
+    __device__ __forceinline__ uint32_t roffsw(int j) const { return (uint32_t)(p[j >> 2] >> (16 * (j & 3))) & 0xFFFFu; }
+    __device__ __forceinline__ uint32_t rpos(int q) const { return (uint32_t)(p[4] >> (8 * q)) & 0xFFu; }
+    // OP_DRUN1 payload (see SwOp::dr): tslot[0] @0, gslot[0] @10, w_off @20, abit[0] @24
+    __device__ __forceinline__ uint32_t d_tslot0() const { return (uint32_t)p[0] & 0xFFFFu; }
+    __device__ __forceinline__ uint32_t d_gslot0() const { return (uint32_t)(p[1] >> 16) & 0xFFFFu; }
+    __device__ __forceinline__ uint32_t d_woff() const { return (uint32_t)(p[2] >> 32) & 0xFFFFu; }
+    __device__ __forceinline__ uint32_t d_abit0() const { return (uint32_t)p[3] & 0xFFu; }
+};
+
+__device__ __forceinline__ OpR fetch_op(const SwOp* __restrict__ ops, int i) {
+    const ulonglong2* w = reinterpret_cast<const ulonglong2*>(ops + i);
+    const ulonglong2 a = w[0], b = w[1], c = w[2], d = w[3], e = w[4], f = w[5];
+    OpR r;
+    r.w0 = (uint32_t)a.x;
+    r.w1 = (uint32_t)(a.x >> 32);
+    r.gmask = a.y;
+    r.gval = b.x;
+    r.p[0] = b.y; r.p[1] = c.x; r.p[2] = c.y; r.p[3] = d.x; r.p[4] = d.y; r.p[5] = e.x; r.p[6] = e.y; r.p[7] = f.x;
+    return r;
+}
+
+template <typename C, bool CTRL, int A>
+__device__ __forceinline__ void op_dense(C (&v)[NREG], const OpR& op, bool tpred) {
     typedef decltype(v[0].x) R;
-    const C m00 = cmake<C, R>((R)op.m[0], (R)op.m[1]), m01 = cmake<C, R>((R)op.m[2], (R)op.m[3]);
-    const C m10 = cmake<C, R>((R)op.m[4], (R)op.m[5]), m11 = cmake<C, R>((R)op.m[6], (R)op.m[7]);
-#define BFLY(A)                                                                   \
-    _Pragma("unroll") for (int j0 = 0; j0 < NREG; ++j0) if (!(j0 & (1 << A))) {   \
-        const int j1 = j0 | (1 << A);                                             \
-        if (!CTRL || (((j0 & op.rmask) == op.rval) && tpred)) {                   \
-            const C a0 = v[j0], a1 = v[j1];                                       \
-            v[j0] = cfma(m01, a1, cmul(m00, a0));                                 \
-            v[j1] = cfma(m11, a1, cmul(m10, a0));                                 \
-        }                                                                         \
-    }
-    switch (op.tgt) {
-        case 0: BFLY(0) break;
-        case 1: BFLY(1) break;
-        case 2: BFLY(2) break;
-        default: BFLY(3) break;
-    }
-#undef BFLY
+    const C m00 = cmake<C, R>((R)op.m(0), (R)op.m(1)), m01 = cmake<C, R>((R)op.m(2), (R)op.m(3));
+    const C m10 = cmake<C, R>((R)op.m(4), (R)op.m(5)), m11 = cmake<C, R>((R)op.m(6), (R)op.m(7));
+    const uint32_t rm = op.rmask(), rv = op.rval();
+#pragma unroll
+    for (int j0 = 0; j0 < NREG; ++j0)
+        if (!(j0 & (1 << A))) {
+            const int j1 = j0 | (1 << A);
+            if (!CTRL || (((j0 & rm) == rv) && tpred)) {
+                const C a0 = v[j0], a1 = v[j1];
+                v[j0] = cfma(m01, a1, cmul(m00, a0));
+                v[j1] = cfma(m11, a1, cmul(m10, a0));
+            }
+        }
 }
 
 // real-entry matrices (H, rotations about y, ...): half the multiplies
-template <typename C, bool CTRL>
-__device__ __forceinline__ void op_dense_real(C (&v)[NREG], const SwOp& op, bool tpred) {
+template <typename C, bool CTRL, int A>
+__device__ __forceinline__ void op_dense_real(C (&v)[NREG], const OpR& op, bool tpred) {
     typedef decltype(v[0].x) R;
-    const R m00 = (R)op.m[0], m01 = (R)op.m[2], m10 = (R)op.m[4], m11 = (R)op.m[6];
-#define BFLYR(A)                                                                  \
-    _Pragma("unroll") for (int j0 = 0; j0 < NREG; ++j0) if (!(j0 & (1 << A))) {   \
-        const int j1 = j0 | (1 << A);                                             \
-        if (!CTRL || (((j0 & op.rmask) == op.rval) && tpred)) {                   \
-            const C a0 = v[j0], a1 = v[j1];                                       \
-            v[j0].x = fma(m01, a1.x, m00 * a0.x);                                 \
-            v[j0].y = fma(m01, a1.y, m00 * a0.y);                                 \
-            v[j1].x = fma(m11, a1.x, m10 * a0.x);                                 \
-            v[j1].y = fma(m11, a1.y, m10 * a0.y);                                 \
-        }                                                                         \
-    }
-    switch (op.tgt) {
-        case 0: BFLYR(0) break;
-        case 1: BFLYR(1) break;
-        case 2: BFLYR(2) break;
-        default: BFLYR(3) break;
-    }
-#undef BFLYR
+    const R m00 = (R)op.m(0), m01 = (R)op.m(2), m10 = (R)op.m(4), m11 = (R)op.m(6);
+    const uint32_t rm = op.rmask(), rv = op.rval();
+#pragma unroll
+    for (int j0 = 0; j0 < NREG; ++j0)
+        if (!(j0 & (1 << A))) {
+            const int j1 = j0 | (1 << A);
+            if (!CTRL || (((j0 & rm) == rv) && tpred)) {
+                const C a0 = v[j0], a1 = v[j1];
+                v[j0].x = fma(m01, a1.x, m00 * a0.x);
+                v[j0].y = fma(m01, a1.y, m00 * a0.y);
+                v[j1].x = fma(m11, a1.x, m10 * a0.x);
+                v[j1].y = fma(m11, a1.y, m10 * a0.y);
+            }
+        }
 }
 
-template <typename C>
-__device__ __forceinline__ void op_permx(C (&v)[NREG], const SwOp& op, bool tpred) {
-#define SWP(A)                                                                    \
-    _Pragma("unroll") for (int j0 = 0; j0 < NREG; ++j0) if (!(j0 & (1 << A))) {   \
-        const int j1 = j0 | (1 << A);                                             \
-        if (((j0 & op.rmask) == op.rval) && tpred) {                              \
-            const C t = v[j0];                                                    \
-            v[j0] = v[j1];                                                        \
-            v[j1] = t;                                                            \
-        }                                                                         \
-    }
-    switch (op.tgt) {
-        case 0: SWP(0) break;
-        case 1: SWP(1) break;
-        case 2: SWP(2) break;
-        default: SWP(3) break;
-    }
-#undef SWP
+template <typename C, int A>
+__device__ __forceinline__ void op_permx(C (&v)[NREG], const OpR& op, bool tpred) {
+    const uint32_t rm = op.rmask(), rv = op.rval();
+#pragma unroll
+    for (int j0 = 0; j0 < NREG; ++j0)
+        if (!(j0 & (1 << A))) {
+            const int j1 = j0 | (1 << A);
+            if (((j0 & rm) == rv) && tpred) {
+                const C t = v[j0];
+                v[j0] = v[j1];
+                v[j1] = t;
+            }
+        }
 }
 
 __device__ __forceinline__ uint32_t expand_rb(uint32_t g, const uint8_t* rpos) {
@@ -186,16 +229,48 @@ __device__ __forceinline__ uint32_t expand_rb(uint32_t g, const uint8_t* rpos) {
     return g;
 }
 
+// single-active-bit phase run with the register-register table folded in:
+// v[j] *= e * W[j] for every register j that has bit A set
+template <typename C, int A>
+__device__ __forceinline__ void drun1(C (&v)[NREG], const double2 e, const double2* __restrict__ w, bool has_w) {
+    typedef decltype(v[0].x) R;
+    if (has_w) {
+#pragma unroll
+        for (int j = 0; j < NREG; ++j)
+            if (j & (1 << A)) {
+                const double2 p = cmul(e, w[j]);
+                v[j] = cmul(v[j], cmake<C, R>((R)p.x, (R)p.y));
+            }
+    } else {
+        const C ee = cmake<C, R>((R)e.x, (R)e.y);
+#pragma unroll
+        for (int j = 0; j < NREG; ++j)
+            if (j & (1 << A)) v[j] = cmul(v[j], ee);
+    }
+}
+
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc) {
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    if (BYTES == 16)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gsrc));
+    else
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+
 template <typename R>
-__global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::type* __restrict__ src,
+__global__ void __launch_bounds__(256, 1) k_sweep(const typename cplx_of<R>::type* __restrict__ src,
                                                   typename cplx_of<R>::type* __restrict__ dst,
                                                   const double* __restrict__ aux,
                                                   const __grid_constant__ SweepParams P) {
     typedef typename cplx_of<R>::type C;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    C* tile = reinterpret_cast<C*>(smem_raw);
     const SweepDesc& D = P.d;
-    double2* smE = reinterpret_cast<double2*>(smem_raw + ((size_t)sizeof(C) << D.k));
+    const size_t tile_bytes = (size_t)sizeof(C) << D.k;
+    auto buf_ptr = [&](int b) { return reinterpret_cast<C*>(smem_raw + (size_t)b * tile_bytes); };
+    double2* smE = reinterpret_cast<double2*>(smem_raw + 2 * tile_bytes);
     double2* smT = smE + MAX_GSLOT;
     const double2* aux2 = reinterpret_cast<const double2*>(aux);
 
@@ -205,10 +280,9 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
     const bool active = tid < n_groups;
     const uint64_t n_tiles = 1ull << (D.n_bits - D.k);
     // per-thread parts of the tile-copy addresses (tile independent)
-    const bool dload = D.direct_load, dstore = D.direct_store;
-    const uint32_t t_ld_l = dload ? expand_rb(tid, D.first_rpos) : tid;
-    const uint64_t t_ld_g = seg_apply64(t_ld_l, D.in_loc);
-    const uint32_t t_ld_s = swz(t_ld_l);
+    const bool dstore = D.direct_store;
+    const uint64_t t_ld_g = seg_apply64(tid, D.in_loc);
+    const uint32_t t_ld_s = swz(tid);
     const uint32_t t_st_l = dstore ? expand_rb(tid, D.last_rpos) : seg_apply(tid, D.st_enum);
     const uint64_t t_st_g = seg_apply64(t_st_l, D.out_loc);
     const uint32_t t_st_s = swz(t_st_l);
@@ -218,115 +292,138 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
     // phase tables of this sweep: global -> shared, once per CTA
     for (uint32_t i = tid; i < D.tab_len; i += blockDim.x) smT[i] = aux2[D.tab_off + i];
 
-    for (uint64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        // ---- tile base addresses ---------------------------------------------------------------
-        uint64_t in_base = 0, out_base = 0;
-        for (int b = 0; b < D.n_glob; ++b) {
-            const uint64_t bit = (t >> b) & 1ull;
-            in_base |= bit << D.in_glob[b];
-            out_base |= bit << D.out_glob[b];
-        }
-        // ---- issue the tile loads first (coalesced 128-bit), then do the per-tile scalars --------
-        C v[NREG];
-        {
-            const uint64_t gb = in_base | t_ld_g;
+    // tile prefetch: 128-bit cp.async straight into the swizzled tile buffer (no registers involved)
+    auto prefetch = [&](uint64_t t, C* buf) {
+        const uint64_t gb = seg_apply64x(t, D.in_glob) | t_ld_g;
 #pragma unroll
-            for (int i = 0; i < NREG; ++i)
-                if (i < n_slots) v[i] = src[gb | D.ld_goff[i]];
-        }
-        for (uint32_t gs = tid; gs < (uint32_t)D.n_gslots; gs += blockDim.x) {
-            const double* gc = aux + D.gcoef_off + (size_t)gs * (1 + D.n_glob);
-            double ang = gc[0];
-            for (int b = 0; b < D.n_glob; ++b)
-                if ((t >> b) & 1ull) ang += gc[1 + b];
-            double sn, cs;
-            sincos(ang, &sn, &cs);
-            smE[gs] = make_double2(cs, sn);
-        }
-        if (!dload) {
-#pragma unroll
-            for (int i = 0; i < NREG; ++i)
-                if (i < n_slots) tile[t_ld_s ^ D.ld_soff[i]] = v[i];
-        }
-        __syncthreads();
+        for (int i = 0; i < NREG; ++i)
+            if (i < n_slots) cp_async<sizeof(C)>(&buf[t_ld_s ^ D.ld_soff[i]], &src[gb | D.ld_goff[i]]);
+    };
 
+    int cur = 0;
+    if (blockIdx.x < n_tiles) prefetch(blockIdx.x, buf_ptr(0));
+    cp_async_commit();
+
+    for (uint64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        C* tile = buf_ptr(cur);
+        // ---- per-tile phase scalars: product of 16-entry chunk tables over the tile id ---------
+        for (uint32_t gs = tid; gs < (uint32_t)D.n_gslots; gs += blockDim.x) {
+            const double2* gt = aux2 + D.gtab_off + (size_t)gs * D.g_chunks * 16;
+            double2 e = gt[t & 15ull];
+            for (int c = 1; c < D.g_chunks; ++c) e = cmul(e, gt[c * 16 + ((t >> (4 * c)) & 15ull)]);
+            smE[gs] = e;
+        }
+        cp_async_wait_all();
+        __syncthreads();  // tile t has landed; per-tile scalars visible; previous tile fully retired
+        {
+            const uint64_t tn = t + gridDim.x;
+            if (tn < n_tiles) prefetch(tn, buf_ptr(cur ^ 1));
+            cp_async_commit();
+        }
+
+        C v[NREG];
         uint32_t base_l = 0, swbase = 0;
-        int cur_stage = -1;
-        bool regs_loaded = dload;
+        bool have_stage = false;
+        uint64_t stq[4] = {0, 0, 0, 0};  // roffsw table of the open stage
+        auto roff_of = [&](int j) { return (uint32_t)(stq[j >> 2] >> (16 * (j & 3))) & 0xFFFFu; };
+        // ops are fetched one ahead so that the constant-bank latency hides behind the previous op's math
+        OpR nxt = fetch_op(P.ops, 0);
         for (int i = 0; i < D.n_ops; ++i) {
-            const SwOp& op = P.ops[i];
-            if (op.type == OP_STAGE) {
-                if (cur_stage >= 0) {
-                    const SwOp& ps = P.ops[cur_stage];
+            const OpR op = nxt;
+            if (i + 1 < D.n_ops) nxt = fetch_op(P.ops, i + 1);
+            const uint32_t type = op.type();
+            if (type == DC_STAGE) {
+                if (have_stage) {
                     if (active) {
 #pragma unroll
-                        for (int j = 0; j < NREG; ++j) tile[swbase ^ ps.st.roffsw[j]] = v[j];
+                        for (int j = 0; j < NREG; ++j) tile[swbase ^ roff_of(j)] = v[j];
                     }
                     __syncthreads();
                 }
-                cur_stage = i;
-                base_l = expand_rb(tid, op.st.rpos);
-                swbase = swz(base_l);
-                if (regs_loaded) {
-                    regs_loaded = false;  // the direct load already put this stage's amplitudes in v[]
-                } else if (active) {
+                have_stage = true;
+                stq[0] = op.p[0]; stq[1] = op.p[1]; stq[2] = op.p[2]; stq[3] = op.p[3];
+                base_l = tid;
 #pragma unroll
-                    for (int j = 0; j < NREG; ++j) v[j] = tile[swbase ^ op.st.roffsw[j]];
+                for (int q = 0; q < RB; ++q) {
+                    const uint32_t pz = op.rpos(q);
+                    base_l = ((base_l >> pz) << (pz + 1)) | (base_l & ((1u << pz) - 1u));
+                }
+                swbase = swz(base_l);
+                if (active) {
+#pragma unroll
+                    for (int j = 0; j < NREG; ++j) v[j] = tile[swbase ^ roff_of(j)];
                 }
                 continue;
             }
-            if ((t & op.gmask) != op.gval) continue;  // control on a global bit not satisfied for this tile
+            if (op.gmask && (t & op.gmask) != op.gval) continue;  // global control not satisfied for this tile
             if (!active) continue;
-            const bool tpred = (base_l & op.lmask) == op.lval;
-            const bool ctrl = (op.rmask | op.lmask) != 0;
-            switch (op.type) {
-                case OP_DENSE: {
-                    const bool real = op.m[1] == 0.0 && op.m[3] == 0.0 && op.m[5] == 0.0 && op.m[7] == 0.0;
-                    if (real) {
-                        if (ctrl) op_dense_real<C, true>(v, op, tpred);
-                        else op_dense_real<C, false>(v, op, true);
-                    } else {
-                        if (ctrl) op_dense<C, true>(v, op, tpred);
-                        else op_dense<C, false>(v, op, true);
+            const bool tpred = (base_l & op.lmask()) == op.lval();
+#define DENSE_CASES(BASE, FN, CTRL)                                   \
+    case BASE + 0: FN<C, CTRL, 0>(v, op, tpred); break;               \
+    case BASE + 1: FN<C, CTRL, 1>(v, op, tpred); break;               \
+    case BASE + 2: FN<C, CTRL, 2>(v, op, tpred); break;               \
+    case BASE + 3: FN<C, CTRL, 3>(v, op, tpred); break;
+            switch (type) {
+                DENSE_CASES(DC_DENSE_REAL_NC, op_dense_real, false)
+                DENSE_CASES(DC_DENSE_CPLX_NC, op_dense, false)
+                DENSE_CASES(DC_DENSE_REAL_C, op_dense_real, true)
+                DENSE_CASES(DC_DENSE_CPLX_C, op_dense, true)
+                case DC_PERMX + 0: op_permx<C, 0>(v, op, tpred); break;
+                case DC_PERMX + 1: op_permx<C, 1>(v, op, tpred); break;
+                case DC_PERMX + 2: op_permx<C, 2>(v, op, tpred); break;
+                case DC_PERMX + 3: op_permx<C, 3>(v, op, tpred); break;
+                case DC_MPHASE: {
+                    const C d = cmake<C, R>((R)op.m(0), (R)op.m(1));
+                    const uint32_t rm = op.rmask(), rv = op.rval();
+#pragma unroll
+                    for (int j = 0; j < NREG; ++j)
+                        if (((j & rm) == rv) && tpred) v[j] = cmul(v[j], d);
+                    break;
+                }
+                case DC_DRUN1 + 0:
+                case DC_DRUN1 + 1:
+                case DC_DRUN1 + 2:
+                case DC_DRUN1 + 3: {
+                    double2 e = make_double2(1.0, 0.0);
+                    const uint32_t gsl = op.d_gslot0(), tsl = op.d_tslot0(), wof = op.d_woff();
+                    if (gsl != NONE16) e = smE[gsl];
+                    if (tsl != NONE16) e = cmul(e, cmul(smT[tsl + (tid & 15u)], smT[tsl + 16u + (tid >> 4)]));
+                    const bool has_w = wof != NONE16;
+                    const double2* w = smT + (has_w ? wof : 0);
+                    switch (type - DC_DRUN1) {
+                        case 0: drun1<C, 0>(v, e, w, has_w); break;
+                        case 1: drun1<C, 1>(v, e, w, has_w); break;
+                        case 2: drun1<C, 2>(v, e, w, has_w); break;
+                        default: drun1<C, 3>(v, e, w, has_w); break;
                     }
                     break;
                 }
-                case OP_PERMX:
-                    op_permx(v, op, tpred);
-                    break;
-                case OP_MPHASE: {
-                    const C d = cmake<C, R>((R)op.m[0], (R)op.m[1]);
-#pragma unroll
-                    for (int j = 0; j < NREG; ++j)
-                        if (((j & op.rmask) == op.rval) && tpred) v[j] = cmul(v[j], d);
-                    break;
-                }
-                case OP_DRUN: {
+                case DC_DRUN: {  // general run (several active bits / thread-wide factor): read from the parameter bank
+                    const SwOp& po = P.ops[i];
                     const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
-                    // thread-wide factor c0
-                    if (op.dr.tslot[RB] != NONE16 || op.dr.gslot[RB] != NONE16) {
+                    if (po.dr.tslot[RB] != NONE16 || po.dr.gslot[RB] != NONE16) {
                         double2 c0 = make_double2(1.0, 0.0);
-                        if (op.dr.gslot[RB] != NONE16) c0 = smE[op.dr.gslot[RB]];
-                        if (op.dr.tslot[RB] != NONE16) c0 = cmul(c0, cmul(smT[op.dr.tslot[RB] + c_lo], smT[op.dr.tslot[RB] + c_hi]));
+                        if (po.dr.gslot[RB] != NONE16) c0 = smE[po.dr.gslot[RB]];
+                        if (po.dr.tslot[RB] != NONE16) c0 = cmul(c0, cmul(smT[po.dr.tslot[RB] + c_lo], smT[po.dr.tslot[RB] + c_hi]));
                         const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
 #pragma unroll
                         for (int j = 0; j < NREG; ++j) v[j] = cmul(v[j], cc);
                     }
-                    for (int s = 0; s < op.dr.n_active; ++s) {
+                    for (int s = 0; s < po.dr.n_active; ++s) {
                         double2 e = make_double2(1.0, 0.0);
-                        if (op.dr.gslot[s] != NONE16) e = smE[op.dr.gslot[s]];
-                        if (op.dr.tslot[s] != NONE16) e = cmul(e, cmul(smT[op.dr.tslot[s] + c_lo], smT[op.dr.tslot[s] + c_hi]));
+                        if (po.dr.gslot[s] != NONE16) e = smE[po.dr.gslot[s]];
+                        if (po.dr.tslot[s] != NONE16) e = cmul(e, cmul(smT[po.dr.tslot[s] + c_lo], smT[po.dr.tslot[s] + c_hi]));
                         const C ee = cmake<C, R>((R)e.x, (R)e.y);
-                        const int bit = 1 << op.dr.abit[s];
+                        const int bit = 1 << po.dr.abit[s];
 #pragma unroll
                         for (int j = 0; j < NREG; ++j)
                             if (j & bit) v[j] = cmul(v[j], ee);
                     }
-                    if (op.dr.w_off != NONE16) {
+                    if (po.dr.w_off != NONE16) {
 #pragma unroll
                         for (int j = 0; j < NREG; ++j)
-                            if ((op.dr.wmask >> j) & 1) {
-                                const double2 w = smT[op.dr.w_off + j];
+                            if ((po.dr.wmask >> j) & 1) {
+                                const double2 w = smT[po.dr.w_off + j];
                                 v[j] = cmul(v[j], cmake<C, R>((R)w.x, (R)w.y));
                             }
                     }
@@ -337,22 +434,20 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
             }
         }
         // ---- store the tile (possibly to a bit-permuted location of the other buffer) ----------
-        if (dstore && cur_stage >= 0) {
-            const uint64_t gb = out_base | t_st_g;
+        const uint64_t gb = seg_apply64x(t, D.out_glob) | t_st_g;
+        if (dstore && have_stage) {
             if (active) {
 #pragma unroll
                 for (int j = 0; j < NREG; ++j) dst[gb | D.st_goff[j]] = v[j];
             }
         } else {
-            if (cur_stage >= 0) {
-                const SwOp& ps = P.ops[cur_stage];
+            if (have_stage) {
                 if (active) {
 #pragma unroll
-                    for (int j = 0; j < NREG; ++j) tile[swbase ^ ps.st.roffsw[j]] = v[j];
+                    for (int j = 0; j < NREG; ++j) tile[swbase ^ roff_of(j)] = v[j];
                 }
                 __syncthreads();
             }
-            const uint64_t gb = out_base | t_st_g;
 #pragma unroll
             for (int i = 0; i < NREG; ++i)
                 if (i < n_slots) v[i] = tile[t_st_s ^ D.st_soff[i]];
@@ -360,8 +455,10 @@ __global__ void __launch_bounds__(256, 2) k_sweep(const typename cplx_of<R>::typ
             for (int i = 0; i < NREG; ++i)
                 if (i < n_slots) dst[gb | D.st_goff[i]] = v[i];
         }
-        __syncthreads();  // shared memory (tile, per-tile scalars) is rewritten by the next tile
+        __syncthreads();  // this buffer and the per-tile scalars are rewritten two / one tiles from now
+        cur ^= 1;
     }
+    cp_async_wait_all();
 }
 
 // ================================================================================================
@@ -395,6 +492,22 @@ void sweep_plan_free(SweepPlan* p) { delete p; }
 static SegMap make_segmap(const std::vector<int>& dst_of_src) {
     // dst_of_src[i] = destination bit of source bit i; merge consecutive runs
     SegMap m;
+    memset(&m, 0, sizeof(m));
+    int i = 0, n = (int)dst_of_src.size();
+    while (i < n) {
+        int j = i + 1;
+        while (j < n && dst_of_src[j] == dst_of_src[j - 1] + 1) ++j;
+        m.src[m.n] = (uint8_t)i;
+        m.len[m.n] = (uint8_t)(j - i);
+        m.dst[m.n] = (uint8_t)dst_of_src[i];
+        ++m.n;
+        i = j;
+    }
+    return m;
+}
+
+static SegMap64 make_segmap64(const std::vector<int>& dst_of_src) {
+    SegMap64 m;
     memset(&m, 0, sizeof(m));
     int i = 0, n = (int)dst_of_src.size();
     while (i < n) {
@@ -694,6 +807,7 @@ struct Builder {
                 op.dr.w_off = (uint16_t)off;
                 op.dr.wmask = wm;
             }
+            if (op.dr.n_active == 1 && op.dr.tslot[RB] == NONE16 && op.dr.gslot[RB] == NONE16) op.type = OP_DRUN1;
             e.ops.push_back(op);
         }
         for (auto& f : fallbacks) e.ops.push_back(f);
@@ -730,9 +844,20 @@ struct Builder {
         D.n_ops = (int)e.ops.size();
         D.n_gslots = (int)e.gslots.size();
         D.n_glob = (int)glob_pos.size();
-        D.gcoef_off = (uint32_t)plan->aux.size();
-        for (auto& s : e.gslots) plan->aux.insert(plan->aux.end(), s.begin(), s.end());
-        if (plan->aux.size() & 1) plan->aux.push_back(0.0);  // keep double2 alignment
+        // per-tile scalars exp(i (c + sum_b coef_b t_b)) as a product of 16-entry tables over 4-bit chunks of the tile id
+        D.g_chunks = std::max(1, (D.n_glob + 3) / 4);
+        D.gtab_off = (uint32_t)(plan->aux.size() / 2);
+        for (auto& gsl : e.gslots)
+            for (int c = 0; c < D.g_chunks; ++c)
+                for (int vv = 0; vv < 16; ++vv) {
+                    double ang = c == 0 ? gsl[0] : 0.0;
+                    for (int q = 0; q < 4; ++q) {
+                        const int b = 4 * c + q;
+                        if (b < D.n_glob && ((vv >> q) & 1)) ang += gsl[1 + b];
+                    }
+                    plan->aux.push_back(std::cos(ang));
+                    plan->aux.push_back(std::sin(ang));
+                }
         D.tab_off = (uint32_t)(plan->aux.size() / 2);
         D.tab_len = (uint32_t)(e.tab.size() / 2);
         plan->aux.insert(plan->aux.end(), e.tab.begin(), e.tab.end());
@@ -754,7 +879,7 @@ struct Builder {
         // leave the lowest local bits to the lanes, so that the accesses stay coalesced
         auto high_only = [](const std::vector<int>& r) { return !r.empty() && r[0] >= 4; };
         static const bool no_direct = getenv("QSV_NO_DIRECT") != nullptr;  // debugging aid
-        D.direct_load = !no_direct && has_work && k >= 9 && high_only(e.first_rloc);
+        D.direct_load = 0;  // (loads always go through the cp.async double buffer)
         D.direct_store = !no_direct && has_work && k >= 9 && !out_of_place && high_only(e.last_rloc);
         for (int q = 0; q < RB; ++q) {
             D.first_rpos[q] = (uint8_t)(e.first_rloc.empty() ? q : e.first_rloc[q]);
@@ -796,11 +921,32 @@ struct Builder {
             D.st_goff[i] = dep(l_st, out_dst);
             D.st_soff[i] = (uint16_t)swz(l_st);
         }
-        for (size_t b = 0; b < glob_pos.size(); ++b) {
-            D.in_glob[b] = (uint8_t)glob_pos[b];
-            D.out_glob[b] = (uint8_t)(out_pos_of_phys ? (*out_pos_of_phys)[glob_pos[b]] : glob_pos[b]);
+        {
+            std::vector<int> gin(glob_pos.size()), gout(glob_pos.size());
+            for (size_t b = 0; b < glob_pos.size(); ++b) {
+                gin[b] = glob_pos[b];
+                gout[b] = out_pos_of_phys ? (*out_pos_of_phys)[glob_pos[b]] : glob_pos[b];
+            }
+            D.in_glob = make_segmap64(gin);
+            D.out_glob = make_segmap64(gout);
         }
-        memcpy(sp->ops, e.ops.data(), e.ops.size() * sizeof(SwOp));
+        for (size_t i = 0; i < e.ops.size(); ++i) {
+            SwOp o = e.ops[i];
+            const bool ctrl = o.rmask || o.lmask;
+            switch (o.type) {  // builder-level kind -> device dispatch code
+                case OP_STAGE: o.type = DC_STAGE; break;
+                case OP_DENSE: {
+                    const bool real = o.m[1] == 0.0 && o.m[3] == 0.0 && o.m[5] == 0.0 && o.m[7] == 0.0;
+                    o.type = (uint8_t)((real ? (ctrl ? DC_DENSE_REAL_C : DC_DENSE_REAL_NC) : (ctrl ? DC_DENSE_CPLX_C : DC_DENSE_CPLX_NC)) + o.tgt);
+                    break;
+                }
+                case OP_PERMX: o.type = (uint8_t)(DC_PERMX + o.tgt); break;
+                case OP_MPHASE: o.type = DC_MPHASE; break;
+                case OP_DRUN1: o.type = (uint8_t)(DC_DRUN1 + o.dr.abit[0]); break;
+                default: o.type = DC_DRUN; break;
+            }
+            sp->ops[i] = o;
+        }
         PlanStep s{};
         s.fused = true;
         s.params = sp;
@@ -944,7 +1090,7 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
         return qsv_fail(ctx, QSV_E_CUDA, "uploading the sweep tables failed: %s", cudaGetErrorString(e));
     }
     // opt in to > 48 KB of dynamic shared memory
-    const int smem = (int)((amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2));
+    const int smem = (int)(2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2));
     if (ctx->dtype == QSV_C128)
         e = cudaFuncSetAttribute(k_sweep<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     else
@@ -972,7 +1118,7 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
     void* other = spare;
     int sm_count = 148;
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
-    const size_t smem = (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2);
+    const size_t smem = 2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2);
     const int threads = std::max(32, 1 << (k - RB));
     const uint64_t n_tiles = 1ull << (n - k);
     int occ = 1;
