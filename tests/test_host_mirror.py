@@ -194,3 +194,45 @@ def test_no_cpu_fallback_without_gpu():
         g.inflate()
     with pytest.raises(_lib.QsvError):
         (g @ qs.CtrlGate(qs.UnivGate.X, [qs.QType.CONTROL1, qs.QType.TARGET])).inflate()
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/quompiler"), reason="the reference tree exists only in the build container")
+def test_builder_accepts_the_reference_own_objects():
+    """Drop-in check: the REAL quompiler CtrlGate/Qubit/QType objects go through B200Builder and the
+    flattener unchanged (duck typing), and give the reference's own value."""
+    import subprocess
+    import sys
+    code = r'''
+import sys, random
+import scipy, sklearn
+import numpy as np
+np.complexfloating = np.complex128
+sys.path.insert(0, "/root/reference"); sys.path.insert(0, %r)
+from functools import reduce
+from quompiler.circuits.qdevice import QDevice
+from quompiler.circuits.qompiler import Qompiler
+from quompiler.config.config_manager import create_config
+from quompiler.construct.bytecode import BytecodeRevIter
+from quompiler.utils.mgen import random_unitary
+import quantum_simulations_b200 as qs
+from oracle import sv_oracle as orc
+random.seed(42); np.random.seed(42)
+u = random_unitary(4)
+cfg = create_config(emit="CTRL_PRUNED", ancilla_offset=100)
+bc = Qompiler(cfg, QDevice(cfg.device)).decompose(u)
+b = qs.B200Builder()
+qs.QRenderer(b).render(bc)                      # our renderer walking the reference's Bytecode tree
+circ = b.finish()
+prog = circ.program()
+n = prog.n_qubits; am = prog.ancilla_mask
+keep = [i for i in range(1 << n) if not (i & am)]
+k = len(keep).bit_length() - 1
+st = np.zeros((1 << n, 1 << k), dtype=np.complex128); st[keep, np.arange(len(keep))] = 1
+flat = st.reshape(-1)
+orc.run_records(prog.records(k), prog.pool(), flat, n + k)
+got = flat.reshape(1 << n, 1 << k)[keep, :]
+assert np.abs(got - u).max() < 1e-10, np.abs(got - u).max()
+print("ok", len(circ), [repr(q) for q in circ.all_qubits()])
+''' % ROOT
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
