@@ -164,6 +164,26 @@ int qsv_permute_bits(qsv_ctx* ctx, const void* in, void* out, int n_bits, const 
 int qsv_compare(qsv_ctx* ctx, const void* a, const void* b, uint64_t n_amps, double rtol,
                 double atol, double* out_max, uint64_t* out_bad, void* stream);
 
+/* Same result as qsv_compare, for callers that must not allocate.  No counterpart in the
+ * reference.  It needs no context and calls no cudaMalloc/cudaFree (nor any routine that does):
+ * its scratch is a fixed array inside the library, about 16 KiB on every GPU that loads
+ * libqsv.so, held until the process exits.  Intended for hosts that have already given all device
+ * memory to their state vectors, or that may not enter the CUDA allocator because it synchronises
+ * the whole device.
+ *  - At most QSV_NOALLOC_MAX_AMPS amplitudes per call; larger sizes return QSV_E_TOOBIG (use
+ *    qsv_compare).  n_amps = 0 returns max = 0, bad = 0.
+ *  - Makes `device` current.  The first call on each device looks up the array's device address
+ *    (a one-off cudaGetSymbolAddress); make that first call before starting any stream capture.
+ *    Not thread-safe against another first call on the same device.
+ *  - All calls on a device share the one array.  Each call overwrites every slot it later
+ *    reads, so contents left by the previous call are harmless; but two calls whose kernels
+ *    overlap on the GPU (different streams, or different host threads) race on it and give
+ *    wrong answers -- serialise them.
+ *  - Synchronises `stream` before returning.  Errors: message via qsv_last_error(NULL).            */
+#define QSV_NOALLOC_MAX_AMPS (1ull << 28)
+int qsv_compare_noalloc(int device, int dtype, const void* a, const void* b, uint64_t n_amps,
+                        double rtol, double atol, double* out_max, uint64_t* out_bad, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -51,7 +51,10 @@ _SIGNATURES = {
     "qsv_permute_bits": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "qsv_compare": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_double,
                               C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_void_p]),
+    "qsv_compare_noalloc": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_double,
+                                      C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_void_p]),
 }
+NOALLOC_MAX_AMPS = 1 << 28
 
 _lib = None
 

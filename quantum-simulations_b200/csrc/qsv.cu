@@ -748,4 +748,69 @@ int qsv_compare(qsv_ctx* ctx, const void* a, const void* b, uint64_t n_amps, dou
     return QSV_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free compare.
+//
+// Same reduction as qsv_compare (k_compare + k_compare_final), but its scratch -- one (max, count)
+// partial per block plus the two results -- lives in the fixed array below instead of memory that
+// qsv_create obtained from cudaMalloc.  It is meant for hosts that cannot go to the CUDA allocator
+// at the moment they need the answer: a simulation that has already sized its state vectors to
+// fill the device (so any further cudaMalloc fails), or a service thread that must not call
+// cudaMalloc/cudaFree because those calls synchronise the whole device and stall every other
+// stream.  The array is part of the library image: each GPU that loads libqsv.so keeps its own
+// 16 KiB copy until the process exits.
+//
+// `g_noalloc_scratch` as written in host code is only a handle for the runtime, not a device
+// address, so the address a kernel can use is looked up once per device with
+// cudaGetSymbolAddress (with that device current) and cached in g_noalloc_ptr[].
+// ------------------------------------------------------------------------------------------------
+#define NOALLOC_BLOCKS 1024
+#define NOALLOC_MAX_DEVICES 64
+static __device__ __align__(256) double g_noalloc_scratch[2 * NOALLOC_BLOCKS + 2];
+static double* g_noalloc_ptr[NOALLOC_MAX_DEVICES];  // per device: address of the array, NULL until first use
+
+int qsv_compare_noalloc(int device, int dtype, const void* a, const void* b, uint64_t n_amps, double rtol, double atol,
+                        double* out_max, uint64_t* out_bad, void* stream) {
+    if (dtype != QSV_C128 && dtype != QSV_C64) return qsv_fail(nullptr, QSV_E_INVALID, "qsv_compare_noalloc: dtype must be QSV_C128 or QSV_C64");
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return qsv_fail(nullptr, QSV_E_INVALID, "qsv_compare_noalloc: device %d out of range", device);
+    if (n_amps > QSV_NOALLOC_MAX_AMPS)
+        return qsv_fail(nullptr, QSV_E_TOOBIG,
+                        "qsv_compare_noalloc: %llu amplitudes exceed the fixed-scratch limit of %llu (QSV_NOALLOC_MAX_AMPS); "
+                        "use qsv_compare with a context for larger arrays",
+                        (unsigned long long)n_amps, (unsigned long long)QSV_NOALLOC_MAX_AMPS);
+    if (n_amps && (!a || !b)) return qsv_fail(nullptr, QSV_E_INVALID, "qsv_compare_noalloc: NULL buffer");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return qsv_fail(nullptr, QSV_E_CUDA, "qsv_compare_noalloc: cudaSetDevice(%d) failed: %s", device, cudaGetErrorString(e));
+    if (!g_noalloc_ptr[device]) {
+        // first call on this device: resolve the device address of the static array (do this before any stream capture)
+        double* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return qsv_fail(nullptr, QSV_E_CUDA, "qsv_compare_noalloc: cudaGetSymbolAddress failed on device %d: %s", device, cudaGetErrorString(e));
+        g_noalloc_ptr[device] = p;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    double res[2] = {0.0, 0.0};
+    if (n_amps) {
+        double* partial = g_noalloc_ptr[device];
+        double* result = partial + 2 * NOALLOC_BLOCKS;
+        const int blocks = (int)std::min<uint64_t>((n_amps + 255) / 256, NOALLOC_BLOCKS);
+        // every slot that k_compare_final reads is written by k_compare in this same call, so nothing
+        // left over from an earlier call needs clearing
+        if (dtype == QSV_C128)
+            k_compare<double><<<blocks, 256, 0, s>>>((const double2*)a, (const double2*)b, n_amps, rtol, atol, partial);
+        else
+            k_compare<float><<<blocks, 256, 0, s>>>((const float2*)a, (const float2*)b, n_amps, rtol, atol, partial);
+        k_compare_final<<<1, 256, 0, s>>>(partial, blocks, result);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaMemcpyAsync(res, result, sizeof(res), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) return qsv_fail(nullptr, QSV_E_CUDA, "qsv_compare_noalloc: %s", cudaGetErrorString(e));
+    }
+    if (out_max) *out_max = res[0];
+    if (out_bad) *out_bad = (uint64_t)res[1];
+    return QSV_OK;
+}
+
 }  // extern "C"
