@@ -536,10 +536,66 @@ struct Builder {
     SweepPlan* plan;
     int n, k, c_low;
     // current sweep
-    std::vector<size_t> cur;  // gate indices
+    std::vector<size_t> cur;  // indices into pg
     uint64_t cur_targets = 0;
+    // SWAP gates (CNOT triples) are pure relabels: pos[b] = physical position that currently holds logical bit b.
+    // Gates are rewritten to physical positions (pg) when they are scheduled.
+    std::vector<qsv_gate_t> pg;
+    int pos[64];
+    struct SwapEvent { size_t first; int a, b; };
+    std::vector<SwapEvent> swaps;      // in program order
+    std::vector<char> consumed;        // gates that belong to a recognised SWAP
+    size_t next_gate = 0;              // index of the next unscheduled source gate (for look-ahead)
+    uint64_t relabelled_gates = 0;
 
-    Builder(qsv_ctx* c, SweepPlan* p, int n_, int k_) : ctx(c), plan(p), n(n_), k(k_) { c_low = (k < n) ? std::min(4, k - 1) : 0; }
+    Builder(qsv_ctx* c, SweepPlan* p, int n_, int k_) : ctx(c), plan(p), n(n_), k(k_) {
+        c_low = (k < n) ? std::min(4, k - 1) : 0;
+        for (int b = 0; b < 64; ++b) pos[b] = b;
+        find_swaps();
+    }
+
+    static bool is_cnot(const qsv_gate_t& g, int* c, int* t) {
+        if (g.kind != QSV_PERMX || g.n_targets != 1) return false;
+        if (__builtin_popcountll(g.ctrl_mask) != 1 || g.ctrl_value != g.ctrl_mask) return false;
+        *c = __builtin_ctzll(g.ctrl_mask);
+        *t = g.target_bits[0];
+        return true;
+    }
+
+    void find_swaps() {
+        const auto& G = ctx->gates;
+        consumed.assign(G.size(), 0);
+        static const bool off = getenv("QSV_NO_RELABEL") != nullptr;  // debugging aid
+        if (off) return;
+        for (size_t i = 0; i + 2 < G.size(); ++i) {
+            int c0, t0, c1, t1, c2, t2;
+            if (is_cnot(G[i], &c0, &t0) && is_cnot(G[i + 1], &c1, &t1) && is_cnot(G[i + 2], &c2, &t2) && c1 == t0 && t1 == c0 &&
+                c2 == c0 && t2 == t0) {
+                swaps.push_back({i, c0, t0});
+                consumed[i] = consumed[i + 1] = consumed[i + 2] = 1;
+                i += 2;
+            }
+        }
+    }
+
+    bool identity_layout() const {
+        for (int b = 0; b < n; ++b)
+            if (pos[b] != b) return false;
+        return true;
+    }
+
+    // rewrite a source gate to the physical positions its bits occupy right now
+    qsv_gate_t to_physical(const qsv_gate_t& g) const {
+        qsv_gate_t r = g;
+        r.ctrl_mask = r.ctrl_value = 0;
+        for (int b = 0; b < n; ++b)
+            if (g.ctrl_mask & (1ull << b)) {
+                r.ctrl_mask |= 1ull << pos[b];
+                if (g.ctrl_value & (1ull << b)) r.ctrl_value |= 1ull << pos[b];
+            }
+        for (uint32_t j = 0; j < g.n_targets; ++j) r.target_bits[j] = (uint8_t)pos[g.target_bits[j]];
+        return r;
+    }
 
     const double* mat(const qsv_gate_t& g) const { return ctx->pool.data() + 2 * g.matrix_offset; }
     static bool is_identity_diag(const double* m) { return m[0] == 1.0 && m[1] == 0.0 && m[6] == 1.0 && m[7] == 0.0; }
@@ -549,9 +605,21 @@ struct Builder {
     bool fits(uint64_t targets) const { return __builtin_popcountll(targets | forced_mask()) <= k; }
 
     int add_gate(size_t gi) {
-        const qsv_gate_t& g = ctx->gates[gi];
-        if (g.kind == QSV_ROWS2 || g.kind == QSV_DENSEK) {
+        next_gate = gi;
+        const qsv_gate_t& src = ctx->gates[gi];
+        if (consumed[gi]) {
+            // first gate of a SWAP triple performs the relabel; the other two are absorbed
+            for (auto& ev : swaps)
+                if (ev.first == gi) std::swap(pos[ev.a], pos[ev.b]);
+            relabelled_gates++;
+            return QSV_OK;
+        }
+        if (src.kind == QSV_ROWS2 || src.kind == QSV_DENSEK) {
+            // not fusable: run as its own kernel on the canonical layout
+            next_gate = gi;
             int rc = flush();
+            if (rc) return rc;
+            rc = restore_layout();
             if (rc) return rc;
             PlanStep s{};
             s.fused = false;
@@ -561,22 +629,63 @@ struct Builder {
             plan->steps.push_back(s);
             return QSV_OK;
         }
-        if (g.kind == QSV_DIAG1) {
-            if (is_identity_diag(mat(g))) {
+        if (src.kind == QSV_DIAG1) {
+            if (is_identity_diag(mat(src))) {
                 plan->dropped_identities++;
                 return QSV_OK;
             }
-            cur.push_back(gi);
+            pg.push_back(to_physical(src));
+            cur.push_back(pg.size() - 1);
             return QSV_OK;
         }
-        const uint64_t tb = 1ull << g.target_bits[0];
+        uint64_t tb = 1ull << pos[src.target_bits[0]];
         if (!fits(cur_targets | tb)) {
-            int rc = flush();
+            int rc = flush();   // may permute the layout
             if (rc) return rc;
+            tb = 1ull << pos[src.target_bits[0]];
         }
         cur_targets |= tb;
-        cur.push_back(gi);
+        pg.push_back(to_physical(src));
+        cur.push_back(pg.size() - 1);
         return QSV_OK;
+    }
+
+    // Data permutation (physical -> physical) that, applied now, makes the layout canonical once all
+    // SWAP relabels from source gate `from` onwards have happened.  Returns false if none is needed.
+    bool pending_permutation(size_t from, std::vector<int>& P) const {
+        int tau[64];
+        for (int b = 0; b < n; ++b) tau[b] = b;
+        for (auto& ev : swaps)
+            if (ev.first >= from) std::swap(tau[ev.a], tau[ev.b]);
+        // at the end logical b would live at pos[tau[b]]; we want it at b
+        P.assign(n, 0);
+        bool any = false;
+        for (int b = 0; b < n; ++b) {
+            P[pos[tau[b]]] = b;
+            any |= pos[tau[b]] != b;
+        }
+        return any;
+    }
+
+    void apply_permutation(const std::vector<int>& P) {
+        for (int b = 0; b < n; ++b) pos[b] = P[pos[b]];
+    }
+
+    // stand-alone permuting sweep (no gates) that restores the canonical layout
+    int restore_layout() {
+        std::vector<int> P;
+        if (!pending_permutation((size_t)-1, P)) return QSV_OK;   // only relabels already made count
+        uint64_t need = forced_mask();
+        for (int p = 0; p < n; ++p)
+            if (P[p] < c_low) need |= 1ull << p;
+        cur_targets = need;  // (2 * c_low <= k always holds: c_low <= 4, k >= 9 whenever c_low == 4)
+        if (__builtin_popcountll(need) > k) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "unsupported: tile too small for the layout restore");
+        choose_tile();
+        Emit e;
+        int rc = push_sweep(e, true, &P);
+        apply_permutation(P);
+        cur_targets = 0;
+        return rc;
     }
 
     // ---- emit one sweep from `cur` ----------------------------------------------------------
@@ -672,7 +781,7 @@ struct Builder {
         std::vector<SwOp> fallbacks;
         auto in_reg = [&](int b) { return loc_of[b] >= 0 && std::find(sc.rloc.begin(), sc.rloc.end(), loc_of[b]) != sc.rloc.end(); };
         for (size_t gi : run) {
-            const qsv_gate_t& g = ctx->gates[gi];
+            const qsv_gate_t& g = pg[gi];
             const double* m = mat(g);
             const int t = g.target_bits[0];
             const double a0 = std::atan2(m[1], m[0]), a1 = std::atan2(m[7], m[6]);
@@ -962,6 +1071,19 @@ struct Builder {
             cur_targets = 0;
             return QSV_OK;
         }
+        // Can the permutation that the remaining SWAP relabels call for ride on this sweep's store?  It can
+        // when the tile also holds the bits that become the low (coalescing) bits of the output.
+        std::vector<int> P;
+        bool fold = false;
+        if (pending_permutation(next_gate, P)) {
+            uint64_t need = cur_targets | forced_mask();
+            for (int p = 0; p < n; ++p)
+                if (P[p] < c_low) need |= 1ull << p;
+            if (__builtin_popcountll(need) <= k) {
+                fold = true;
+                cur_targets = need;
+            }
+        }
         choose_tile();
         Emit e;
         StageCtx sc;
@@ -973,7 +1095,7 @@ struct Builder {
             want.clear();
             size_t j = i;
             for (; j < cur.size(); ++j) {
-                const qsv_gate_t& g = ctx->gates[cur[j]];
+                const qsv_gate_t& g = pg[cur[j]];
                 if (g.kind == QSV_DIAG1) continue;
                 const int l = loc_of[g.target_bits[0]];
                 if (std::find(want.begin(), want.end(), l) != want.end()) continue;
@@ -983,7 +1105,7 @@ struct Builder {
             // diagonal gates prefer a register bit of their own: if the stage has room, give pair gates one
             if ((int)want.size() < RB) {
                 for (size_t q = i; q < j && (int)want.size() < RB; ++q) {
-                    const qsv_gate_t& g = ctx->gates[cur[q]];
+                    const qsv_gate_t& g = pg[cur[q]];
                     if (g.kind != QSV_DIAG1 || __builtin_popcountll(g.ctrl_mask) != 1) continue;
                     const int t = g.target_bits[0], cb = __builtin_ctzll(g.ctrl_mask);
                     auto has = [&](int b) { return loc_of[b] >= 0 && std::find(want.begin(), want.end(), loc_of[b]) != want.end(); };
@@ -1013,7 +1135,7 @@ struct Builder {
             std::vector<size_t> run;
             const size_t RUN_CHUNK = 64;
             for (size_t q = i; q < j; ++q) {
-                const qsv_gate_t& g = ctx->gates[cur[q]];
+                const qsv_gate_t& g = pg[cur[q]];
                 if (g.kind == QSV_DIAG1) {
                     run.push_back(cur[q]);
                     if (run.size() >= RUN_CHUNK) {
@@ -1047,7 +1169,8 @@ struct Builder {
             }
             i = j;
         }
-        int rc = push_sweep(e, false, nullptr);
+        int rc = push_sweep(e, fold, fold ? &P : nullptr);
+        if (fold) apply_permutation(P);
         cur.clear();
         cur_targets = 0;
         return rc;
@@ -1078,11 +1201,14 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
             return rc;
         }
     }
+    b.next_gate = ctx->gates.size();
     int rc = b.flush();
+    if (!rc) rc = b.restore_layout();
     if (rc) {
         delete plan;
         return rc;
     }
+    plan->dropped_identities += b.relabelled_gates;  // counted as applied source gates
     cudaError_t e = cudaMalloc(&plan->d_aux, plan->aux.size() * sizeof(double));
     if (e == cudaSuccess) e = cudaMemcpy(plan->d_aux, plan->aux.data(), plan->aux.size() * sizeof(double), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) {

@@ -129,6 +129,40 @@ def test_random_circuit_vs_oracle(seed, fuse):
     assert np.abs(got - want).max() < TOL128
 
 
+@pytest.mark.parametrize("n,batch", [(9, 2), (14, 1), (15, 4)])
+def test_swaps_are_relabelled_and_layout_is_restored(n, batch):
+    """SWAPs written as CNOT triples in the middle and at the end of a circuit: the fused plan treats them
+    as bit relabels (permuting store) and must hand back the canonical layout."""
+    random.seed(n)
+    np.random.seed(n)
+    q = [qs.Qubit(i) for i in range(n)]
+
+    def swap(a, b):
+        return [qs.CtrlGate(qs.UnivGate.X, [C1, T], [q[a], q[b]]), qs.CtrlGate(qs.UnivGate.X, [T, C1], [q[a], q[b]]),
+                qs.CtrlGate(qs.UnivGate.X, [C1, T], [q[a], q[b]])]
+
+    def some_gates(m):
+        out = []
+        for _ in range(m):
+            g = random_ctrlgate(random.randint(1, 3), 1, qnum=n)
+            if random.random() < 0.4:
+                g = qs.CtrlGate(np.diag(np.exp(1j * np.random.uniform(0, 6.28, 2))), g.controls(), g.qspace)
+            out.append(g)
+        return out
+
+    gates = some_gates(12) + swap(0, n - 1) + some_gates(10) + swap(2, n - 2) + swap(1, 3) + some_gates(10) + swap(n - 1, 1)
+    prog = flatten(gates, q)
+    x = np.stack([random_state(1 << n) for _ in range(batch)], axis=1)
+    eng = get_engine()
+    eng.reset_stats()
+    got = apply_circuit(prog, x, fuse=True)
+    st = eng.stats()
+    assert st["fused_sweeps"] > 0 and st["gates_applied"] == len(gates)
+    want = orc.simulate(gates, q, x)
+    assert np.abs(got - want).max() < TOL128
+    assert np.abs(apply_circuit(prog, x, fuse=False) - want).max() < TOL128
+
+
 def test_builder_conformance_template():
     """The five checks of the reference's CircuitTestTemplate (circuit_test_template.py:21-113), with
     the expected matrices taken from the oracle's restatement of inflate()."""
@@ -287,7 +321,8 @@ def test_large_state_properties():
         eng.upload(prog, 0)
         if fuse:
             eng.fuse()
-        back = eng.run(res, spare if spare is not None else None)
+        other = None if spare is None else (st if res is spare else spare)   # the buffer that does not hold `res`
+        back = eng.run(res, other)
         assert abs(complex(back[0]) - 1.0) < 1e-10
         assert float(back[1:].abs().max()) < 1e-10
         del spare
