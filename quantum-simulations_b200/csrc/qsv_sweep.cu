@@ -37,11 +37,11 @@
 #define NREG 16
 #define MAX_OPS 320      // ops per launch (kernel parameter space, 32 KB limit)
 #define MAX_GSLOT 96     // per-tile phase scalars per launch
-#define MAX_TAB 1024     // double2 entries of phase tables per launch (16 KB of shared memory)
+#define MAX_TAB 512      // double2 entries of phase tables per launch (8 KB of shared memory)
 #define TSLOT_LEN 32     // one thread-phase slot = 2 chunks x 16 entries
 #define MAX_SEG 12
 
-enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_DRUN = 4, OP_DRUN1 = 5 };
+enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_W = 4, OP_TWID = 5, OP_HADD = 6 };
 // Dispatch codes (SwOp::type as stored): the host resolves op kind, target register bit, real/complex
 // and controlled/uncontrolled into ONE small integer so that the device decodes an op with a single
 // jump-table branch.
@@ -52,9 +52,10 @@ enum : uint8_t {
     DC_DENSE_REAL_C = 9,
     DC_DENSE_CPLX_C = 13,
     DC_PERMX = 17,
-    DC_DRUN1 = 21,           // +active register bit
+    DC_HADD = 21,            // +tgt: unnormalised Hadamard butterfly (a0+a1, a0-a1); the 1/sqrt2 is folded into a later OP_TWID
     DC_MPHASE = 25,
-    DC_DRUN = 26,
+    DC_W = 26,               // register-register phase table: v[j] *= W[j]
+    DC_TWID = 27,            // deferred per-register-bit phases (thread / tile dependent) + thread-wide factor + real scale
 };
 enum : uint8_t { FLAG_REAL = 1 };
 #define NONE16 0xFFFFu
@@ -71,14 +72,17 @@ struct __align__(16) SwOp {  // 96 bytes = 6 x 16 B, fetched one op ahead into r
             uint8_t rpos[RB];        // local bit positions of the register bits, ascending
             uint8_t flags;
         } st;
-        struct {                     // OP_DRUN
-            uint16_t tslot[RB + 1];  // thread-phase slot (offset into the shared tables) per active bit, [RB] = c0
-            uint16_t gslot[RB + 1];  // per-tile scalar slot per active bit, [RB] = c0
-            uint16_t w_off;          // W table offset (16 entries) or NONE16
+        struct {                     // OP_W
+            uint16_t w_off;          // W table offset (16 entries) in the shared tables
             uint16_t wmask;          // registers j with W[j] != 1
-            uint8_t abit[RB];        // register bit index of each active slot
+        } w;
+        struct {                     // OP_TWID
+            double scale;            // real factor applied to every register (1.0 = none)
+            uint16_t tslot[RB + 1];  // thread-phase slot (offset into the shared tables) per listed bit, [RB] = thread-wide factor
+            uint16_t gslot[RB + 1];  // per-tile scalar slot per listed bit, [RB] = thread-wide factor
+            uint8_t abit[RB];        // register bit index of each listed slot
             uint8_t n_active;
-        } dr;
+        } tw;
     };
 };
 static_assert(sizeof(SwOp) == 96, "SwOp layout");
@@ -148,11 +152,14 @@ struct OpR {
     // OP_STAGE payload: roffsw[16] (u16) then rpos[4] (u8)
     __device__ __forceinline__ uint32_t roffsw(int j) const { return (uint32_t)(p[j >> 2] >> (16 * (j & 3))) & 0xFFFFu; }
     __device__ __forceinline__ uint32_t rpos(int q) const { return (uint32_t)(p[4] >> (8 * q)) & 0xFFu; }
-    // OP_DRUN1 payload (see SwOp::dr): tslot[0] @0, gslot[0] @10, w_off @20, abit[0] @24
-    __device__ __forceinline__ uint32_t d_tslot0() const { return (uint32_t)p[0] & 0xFFFFu; }
-    __device__ __forceinline__ uint32_t d_gslot0() const { return (uint32_t)(p[1] >> 16) & 0xFFFFu; }
-    __device__ __forceinline__ uint32_t d_woff() const { return (uint32_t)(p[2] >> 32) & 0xFFFFu; }
-    __device__ __forceinline__ uint32_t d_abit0() const { return (uint32_t)p[3] & 0xFFu; }
+    // generic little-endian field access into the payload (offsets are compile-time constants)
+    __device__ __forceinline__ uint32_t u16_at(int off) const { return (uint32_t)(p[off >> 3] >> (8 * (off & 7))) & 0xFFFFu; }
+    __device__ __forceinline__ uint32_t u8_at(int off) const { return (uint32_t)(p[off >> 3] >> (8 * (off & 7))) & 0xFFu; }
+    // OP_W payload: w_off @0, wmask @2.  OP_TWID payload: scale @0, tslot[s] @8+2s, gslot[s] @8+2(RB+1)+2s, abit[s] @8+4(RB+1)+s, n_active after
+    __device__ __forceinline__ uint32_t tw_tslot(int s_) const { return u16_at(8 + 2 * s_); }
+    __device__ __forceinline__ uint32_t tw_gslot(int s_) const { return u16_at(8 + 2 * (RB + 1) + 2 * s_); }
+    __device__ __forceinline__ uint32_t tw_abit(int s_) const { return u8_at(8 + 4 * (RB + 1) + s_); }
+    __device__ __forceinline__ uint32_t tw_n() const { return u8_at(8 + 4 * (RB + 1) + RB); }
 };
 
 __device__ __forceinline__ OpR fetch_op(const SwOp* __restrict__ ops, int i) {
@@ -229,24 +236,29 @@ __device__ __forceinline__ uint32_t expand_rb(uint32_t g, const uint8_t* rpos) {
     return g;
 }
 
-// single-active-bit phase run with the register-register table folded in:
-// v[j] *= e * W[j] for every register j that has bit A set
+// unnormalised Hadamard butterfly on register bit A: (a0, a1) -> (a0 + a1, a0 - a1)
 template <typename C, int A>
-__device__ __forceinline__ void drun1(C (&v)[NREG], const double2 e, const double2* __restrict__ w, bool has_w) {
+__device__ __forceinline__ void op_hadd(C (&v)[NREG]) {
+#pragma unroll
+    for (int j0 = 0; j0 < NREG; ++j0)
+        if (!(j0 & (1 << A))) {
+            const int j1 = j0 | (1 << A);
+            const C a0 = v[j0], a1 = v[j1];
+            v[j0].x = a0.x + a1.x;
+            v[j0].y = a0.y + a1.y;
+            v[j1].x = a0.x - a1.x;
+            v[j1].y = a0.y - a1.y;
+        }
+}
+
+// v[j] *= e for every register j that has bit A set
+template <typename C, int A>
+__device__ __forceinline__ void mul_bit(C (&v)[NREG], const double2 e) {
     typedef decltype(v[0].x) R;
-    if (has_w) {
+    const C ee = cmake<C, R>((R)e.x, (R)e.y);
 #pragma unroll
-        for (int j = 0; j < NREG; ++j)
-            if (j & (1 << A)) {
-                const double2 p = cmul(e, w[j]);
-                v[j] = cmul(v[j], cmake<C, R>((R)p.x, (R)p.y));
-            }
-    } else {
-        const C ee = cmake<C, R>((R)e.x, (R)e.y);
-#pragma unroll
-        for (int j = 0; j < NREG; ++j)
-            if (j & (1 << A)) v[j] = cmul(v[j], ee);
-    }
+    for (int j = 0; j < NREG; ++j)
+        if (j & (1 << A)) v[j] = cmul(v[j], ee);
 }
 
 template <int BYTES>
@@ -260,8 +272,10 @@ __device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
-template <typename R>
-__global__ void __launch_bounds__(256, 1) k_sweep(const typename cplx_of<R>::type* __restrict__ src,
+// Two instantiations: <256, 1> for 64 KB tiles (k = 12, one CTA per SM) and <128, 3> for smaller tiles
+// (register cap 168 so that three double-buffered 32 KB-tile CTAs share an SM).
+template <typename R, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>::type* __restrict__ src,
                                                   typename cplx_of<R>::type* __restrict__ dst,
                                                   const double* __restrict__ aux,
                                                   const __grid_constant__ SweepParams P) {
@@ -380,52 +394,58 @@ __global__ void __launch_bounds__(256, 1) k_sweep(const typename cplx_of<R>::typ
                         if (((j & rm) == rv) && tpred) v[j] = cmul(v[j], d);
                     break;
                 }
-                case DC_DRUN1 + 0:
-                case DC_DRUN1 + 1:
-                case DC_DRUN1 + 2:
-                case DC_DRUN1 + 3: {
-                    double2 e = make_double2(1.0, 0.0);
-                    const uint32_t gsl = op.d_gslot0(), tsl = op.d_tslot0(), wof = op.d_woff();
-                    if (gsl != NONE16) e = smE[gsl];
-                    if (tsl != NONE16) e = cmul(e, cmul(smT[tsl + (tid & 15u)], smT[tsl + 16u + (tid >> 4)]));
-                    const bool has_w = wof != NONE16;
-                    const double2* w = smT + (has_w ? wof : 0);
-                    switch (type - DC_DRUN1) {
-                        case 0: drun1<C, 0>(v, e, w, has_w); break;
-                        case 1: drun1<C, 1>(v, e, w, has_w); break;
-                        case 2: drun1<C, 2>(v, e, w, has_w); break;
-                        default: drun1<C, 3>(v, e, w, has_w); break;
-                    }
+                case DC_HADD + 0: op_hadd<C, 0>(v); break;
+                case DC_HADD + 1: op_hadd<C, 1>(v); break;
+                case DC_HADD + 2: op_hadd<C, 2>(v); break;
+                case DC_HADD + 3: op_hadd<C, 3>(v); break;
+                case DC_W: {
+                    const double2* w = smT + op.u16_at(0);
+                    const uint32_t wm = op.u16_at(2);
+#pragma unroll
+                    for (int j = 0; j < NREG; ++j)
+                        if ((wm >> j) & 1) {
+                            const double2 ww = w[j];
+                            v[j] = cmul(v[j], cmake<C, R>((R)ww.x, (R)ww.y));
+                        }
                     break;
                 }
-                case DC_DRUN: {  // general run (several active bits / thread-wide factor): read from the parameter bank
-                    const SwOp& po = P.ops[i];
+                case DC_TWID: {
                     const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
-                    if (po.dr.tslot[RB] != NONE16 || po.dr.gslot[RB] != NONE16) {
-                        double2 c0 = make_double2(1.0, 0.0);
-                        if (po.dr.gslot[RB] != NONE16) c0 = smE[po.dr.gslot[RB]];
-                        if (po.dr.tslot[RB] != NONE16) c0 = cmul(c0, cmul(smT[po.dr.tslot[RB] + c_lo], smT[po.dr.tslot[RB] + c_hi]));
+                    const double scale = op.m(0);
+                    const uint32_t ts0 = op.tw_tslot(RB), gs0 = op.tw_gslot(RB);
+                    if (ts0 != NONE16 || gs0 != NONE16) {  // thread-wide complex factor (times the scale)
+                        double2 c0 = make_double2(scale, 0.0);
+                        if (gs0 != NONE16) {
+                            const double2 g0 = smE[gs0];
+                            c0 = make_double2(scale * g0.x, scale * g0.y);
+                        }
+                        if (ts0 != NONE16) c0 = cmul(c0, cmul(smT[ts0 + c_lo], smT[ts0 + c_hi]));
                         const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
 #pragma unroll
                         for (int j = 0; j < NREG; ++j) v[j] = cmul(v[j], cc);
-                    }
-                    for (int s = 0; s < po.dr.n_active; ++s) {
-                        double2 e = make_double2(1.0, 0.0);
-                        if (po.dr.gslot[s] != NONE16) e = smE[po.dr.gslot[s]];
-                        if (po.dr.tslot[s] != NONE16) e = cmul(e, cmul(smT[po.dr.tslot[s] + c_lo], smT[po.dr.tslot[s] + c_hi]));
-                        const C ee = cmake<C, R>((R)e.x, (R)e.y);
-                        const int bit = 1 << po.dr.abit[s];
+                    } else if (scale != 1.0) {
+                        const R sc = (R)scale;
 #pragma unroll
-                        for (int j = 0; j < NREG; ++j)
-                            if (j & bit) v[j] = cmul(v[j], ee);
+                        for (int j = 0; j < NREG; ++j) {
+                            v[j].x *= sc;
+                            v[j].y *= sc;
+                        }
                     }
-                    if (po.dr.w_off != NONE16) {
+                    const uint32_t na = op.tw_n();
 #pragma unroll
-                        for (int j = 0; j < NREG; ++j)
-                            if ((po.dr.wmask >> j) & 1) {
-                                const double2 w = smT[po.dr.w_off + j];
-                                v[j] = cmul(v[j], cmake<C, R>((R)w.x, (R)w.y));
+                    for (int s_ = 0; s_ < RB; ++s_) {
+                        if ((uint32_t)s_ < na) {
+                            double2 e = make_double2(1.0, 0.0);
+                            const uint32_t gsl = op.tw_gslot(s_), tsl = op.tw_tslot(s_);
+                            if (gsl != NONE16) e = smE[gsl];
+                            if (tsl != NONE16) e = cmul(e, cmul(smT[tsl + c_lo], smT[tsl + c_hi]));
+                            switch (op.tw_abit(s_)) {
+                                case 0: mul_bit<C, 0>(v, e); break;
+                                case 1: mul_bit<C, 1>(v, e); break;
+                                case 2: mul_bit<C, 2>(v, e); break;
+                                default: mul_bit<C, 3>(v, e); break;
                             }
+                        }
                     }
                     break;
                 }
@@ -774,9 +794,9 @@ struct Builder {
         e.ops.push_back(op);
     }
 
-    // close a run of diagonal gates: emit DRUN (+ MPHASE fallbacks)
-    void emit_diag_run(Emit& e, const StageCtx& sc, const std::vector<size_t>& run) {
-        if (run.empty()) return;
+    // close a run of diagonal gates: register-register phases -> OP_W now, everything else -> deferred (Pending)
+    int emit_diag_run(Emit& e, const StageCtx& sc, const std::vector<size_t>& run) {
+        if (run.empty()) return QSV_OK;
         Poly P;
         std::vector<SwOp> fallbacks;
         auto in_reg = [&](int b) { return loc_of[b] >= 0 && std::find(sc.rloc.begin(), sc.rloc.end(), loc_of[b]) != sc.rloc.end(); };
@@ -823,21 +843,8 @@ struct Builder {
             e.n_gates++;
         }
         if (!P.empty()) {
-            SwOp op;
-            memset(&op, 0, sizeof(op));
-            op.type = OP_DRUN;
-            for (int s = 0; s <= RB; ++s) {
-                op.dr.tslot[s] = NONE16;
-                op.dr.gslot[s] = NONE16;
-            }
-            op.dr.w_off = NONE16;
+            // classify the polynomial's terms for this stage
             const int n_thr = (int)sc.tloc.size();
-            // per register bit: const, thread-bit coefs, global-bit coefs
-            double rc[RB] = {0, 0, 0, 0};
-            std::vector<std::vector<double>> rt(RB, std::vector<double>(n_thr, 0.0)), rg(RB, std::vector<double>(glob_pos.size(), 0.0));
-            double c0 = P.t0;
-            std::vector<double> ct(n_thr, 0.0), cg(glob_pos.size(), 0.0);
-            double w[RB][RB] = {{0}};
             auto reg_index = [&](int b) -> int {
                 if (loc_of[b] < 0) return -1;
                 auto it = std::find(sc.rloc.begin(), sc.rloc.end(), loc_of[b]);
@@ -848,78 +855,166 @@ struct Builder {
                 auto it = std::find(sc.tloc.begin(), sc.tloc.end(), loc_of[b]);
                 return it == sc.tloc.end() ? -1 : (int)(it - sc.tloc.begin());
             };
+            pend.ensure_size(n_thr, (int)glob_pos.size());
+            pend.c0.cst += P.t0;
+            pend.c0.any |= P.t0 != 0;
+            double w[RB][RB] = {{0}};
             for (auto& kv : P.a) {
                 const int b = kv.first;
                 const int ri = reg_index(b);
-                if (ri >= 0) rc[ri] += kv.second;
-                else if (thr_index(b) >= 0) ct[thr_index(b)] += kv.second;
-                else cg[glob_of[b]] += kv.second;
+                Pending::Term& tm = ri >= 0 ? pend.bit[ri] : pend.c0;
+                if (ri >= 0) tm.cst += kv.second;
+                else if (thr_index(b) >= 0) tm.thr[thr_index(b)] += kv.second;
+                else tm.glb[glob_of[b]] += kv.second;
+                tm.any = true;
             }
+            bool has_w = false;
             for (auto& kv : P.b) {
                 const int b1 = kv.first.first, b2 = kv.first.second;
-                int r1 = reg_index(b1), r2 = reg_index(b2);
+                const int r1 = reg_index(b1), r2 = reg_index(b2);
                 if (r1 >= 0 && r2 >= 0) {
                     w[std::min(r1, r2)][std::max(r1, r2)] += kv.second;
+                    has_w = true;
                 } else {
                     const int ri = r1 >= 0 ? r1 : r2;
                     const int ob = r1 >= 0 ? b2 : b1;
-                    if (thr_index(ob) >= 0) rt[ri][thr_index(ob)] += kv.second;
-                    else rg[ri][glob_of[ob]] += kv.second;
+                    if (thr_index(ob) >= 0) pend.bit[ri].thr[thr_index(ob)] += kv.second;
+                    else pend.bit[ri].glb[glob_of[ob]] += kv.second;
+                    pend.bit[ri].any = true;
                 }
             }
-            auto any = [](const std::vector<double>& x) { return std::any_of(x.begin(), x.end(), [](double d) { return d != 0; }); };
-            auto make_table = [&](const std::vector<double>& coef) -> uint16_t {
-            // two 16-entry tables over the low / high 4-bit chunk of the thread id
-                const size_t off = e.tab.size() / 2;
-                e.tab.resize(e.tab.size() + 2 * TSLOT_LEN);
-                for (int chunk = 0; chunk < 2; ++chunk)
-                    for (int vv = 0; vv < 16; ++vv) {
-                        double ang = 0;
-                        for (int q = 0; q < 4; ++q) {
-                            const int tb_i = chunk * 4 + q;
-                            if (tb_i < n_thr && ((vv >> q) & 1)) ang += coef[tb_i];
-                        }
-                        e.tab[2 * (off + chunk * 16 + vv)] = std::cos(ang);
-                        e.tab[2 * (off + chunk * 16 + vv) + 1] = std::sin(ang);
-                    }
-                return (uint16_t)off;
-            };
-            // c0
-            if (any(ct)) op.dr.tslot[RB] = make_table(ct);
-            if (c0 != 0 || any(cg)) op.dr.gslot[RB] = (uint16_t)new_gslot(e, c0, cg);
-            int na = 0;
-            for (int ri = 0; ri < RB; ++ri) {
-                const bool has_t = any(rt[ri]), has_g = rc[ri] != 0 || any(rg[ri]);
-                if (!has_t && !has_g) continue;
-                op.dr.abit[na] = (uint8_t)ri;
-                if (has_t) op.dr.tslot[na] = make_table(rt[ri]);
-                if (has_g) op.dr.gslot[na] = (uint16_t)new_gslot(e, rc[ri], rg[ri]);
-                ++na;
-            }
-            op.dr.n_active = (uint8_t)na;
-            bool has_w = false;
-            for (int i = 0; i < RB; ++i)
-                for (int j = i + 1; j < RB; ++j) has_w |= w[i][j] != 0;
             if (has_w) {
+                // register-register terms do not commute with later butterflies on those bits: apply them here
+                int rc = ensure_budget(e, sc, 1, 0, NREG);
+                if (rc) return rc;
                 const size_t off = e.tab.size() / 2;
                 e.tab.resize(e.tab.size() + 2 * NREG);
                 uint16_t wm = 0;
                 for (int j = 0; j < NREG; ++j) {
                     double ang = 0;
-                    for (int p = 0; p < RB; ++p)
-                        for (int q = p + 1; q < RB; ++q)
-                            if (((j >> p) & 1) && ((j >> q) & 1)) ang += w[p][q];
+                    for (int p_ = 0; p_ < RB; ++p_)
+                        for (int q = p_ + 1; q < RB; ++q)
+                            if (((j >> p_) & 1) && ((j >> q) & 1)) ang += w[p_][q];
                     e.tab[2 * (off + j)] = std::cos(ang);
                     e.tab[2 * (off + j) + 1] = std::sin(ang);
                     if (ang != 0) wm |= (uint16_t)(1u << j);
                 }
-                op.dr.w_off = (uint16_t)off;
-                op.dr.wmask = wm;
+                SwOp op;
+                memset(&op, 0, sizeof(op));
+                op.type = OP_W;
+                op.w.w_off = (uint16_t)off;
+                op.w.wmask = wm;
+                e.ops.push_back(op);
             }
-            if (op.dr.n_active == 1 && op.dr.tslot[RB] == NONE16 && op.dr.gslot[RB] == NONE16) op.type = OP_DRUN1;
-            e.ops.push_back(op);
         }
-        for (auto& f : fallbacks) e.ops.push_back(f);
+        if (!fallbacks.empty()) {
+            int rc = ensure_budget(e, sc, fallbacks.size(), 0, 0);
+            if (rc) return rc;
+            for (auto& f : fallbacks) e.ops.push_back(f);
+        }
+        return QSV_OK;
+    }
+
+    // Deferred phases of the open stage.  A factor exp(i x_a (c + sum thread/tile terms)) on register bit a
+    // commutes with everything that follows in the stage except a butterfly/swap on bit a itself, so it is
+    // accumulated here (angles add) and applied once, by OP_TWID, at the latest possible point.
+    struct Pending {
+        struct Term {
+            double cst = 0;
+            std::vector<double> thr, glb;
+            bool any = false;
+            void clear() {
+                cst = 0;
+                std::fill(thr.begin(), thr.end(), 0.0);
+                std::fill(glb.begin(), glb.end(), 0.0);
+                any = false;
+            }
+        };
+        Term bit[RB], c0;
+        void ensure_size(int n_thr, int n_glob) {
+            for (int i = 0; i <= RB; ++i) {
+                Term& t = i < RB ? bit[i] : c0;
+                if ((int)t.thr.size() != n_thr) t.thr.assign(n_thr, 0.0);
+                if ((int)t.glb.size() != n_glob) t.glb.assign(n_glob, 0.0);
+            }
+        }
+    } pend;
+    double sweep_scale = 1.0;  // product of the 1/sqrt2 factors owed by unnormalised butterflies
+
+    static bool nz(const std::vector<double>& x) { return std::any_of(x.begin(), x.end(), [](double d) { return d != 0; }); }
+
+    // make room in the current launch; if it is full, close it and reopen the same stage in a new one
+    int ensure_budget(Emit& e, const StageCtx& sc, size_t ops_needed, size_t slots_needed, size_t tab_needed) {
+        if (e.ops.size() + ops_needed > MAX_OPS || e.gslots.size() + slots_needed > MAX_GSLOT || e.tab.size() / 2 + tab_needed > MAX_TAB) {
+            int rc = push_sweep(e, false, nullptr);
+            if (rc) return rc;
+            emit_stage_op(e, sc);
+        }
+        return QSV_OK;
+    }
+
+    uint16_t make_thread_table(Emit& e, const std::vector<double>& coef) {
+        // two 16-entry tables over the low / high 4-bit chunk of the thread id
+        const int n_thr = (int)coef.size();
+        const size_t off = e.tab.size() / 2;
+        e.tab.resize(e.tab.size() + 2 * TSLOT_LEN);
+        for (int chunk = 0; chunk < 2; ++chunk)
+            for (int vv = 0; vv < 16; ++vv) {
+                double ang = 0;
+                for (int q = 0; q < 4; ++q) {
+                    const int tb_i = chunk * 4 + q;
+                    if (tb_i < n_thr && ((vv >> q) & 1)) ang += coef[tb_i];
+                }
+                e.tab[2 * (off + chunk * 16 + vv)] = std::cos(ang);
+                e.tab[2 * (off + chunk * 16 + vv) + 1] = std::sin(ang);
+            }
+        return (uint16_t)off;
+    }
+
+    // emit OP_TWID for the register bits in `mask` (and, if with_c0, the thread-wide factor and the owed scale)
+    int flush_pending(Emit& e, const StageCtx& sc, unsigned mask, bool with_c0) {
+        size_t slots = 0, tabs = 0;
+        int na = 0;
+        for (int ri = 0; ri < RB; ++ri)
+            if (((mask >> ri) & 1) && pend.bit[ri].any) {
+                ++na;
+                if (nz(pend.bit[ri].thr)) tabs += TSLOT_LEN;
+                if (pend.bit[ri].cst != 0 || nz(pend.bit[ri].glb)) ++slots;
+            }
+        const bool c0_on = with_c0 && pend.c0.any;
+        const bool scale_on = with_c0 && sweep_scale != 1.0;
+        if (c0_on) {
+            if (nz(pend.c0.thr)) tabs += TSLOT_LEN;
+            if (pend.c0.cst != 0 || nz(pend.c0.glb)) ++slots;
+        }
+        if (na == 0 && !c0_on && !scale_on) return QSV_OK;
+        int rc = ensure_budget(e, sc, 1, slots, tabs);
+        if (rc) return rc;
+        SwOp op;
+        memset(&op, 0, sizeof(op));
+        op.type = OP_TWID;
+        op.tw.scale = scale_on ? sweep_scale : 1.0;
+        if (scale_on) sweep_scale = 1.0;
+        for (int s_ = 0; s_ <= RB; ++s_) op.tw.tslot[s_] = op.tw.gslot[s_] = NONE16;
+        int k_ = 0;
+        for (int ri = 0; ri < RB; ++ri)
+            if (((mask >> ri) & 1) && pend.bit[ri].any) {
+                Pending::Term& t = pend.bit[ri];
+                op.tw.abit[k_] = (uint8_t)ri;
+                if (nz(t.thr)) op.tw.tslot[k_] = make_thread_table(e, t.thr);
+                if (t.cst != 0 || nz(t.glb)) op.tw.gslot[k_] = (uint16_t)new_gslot(e, t.cst, t.glb);
+                t.clear();
+                ++k_;
+            }
+        op.tw.n_active = (uint8_t)k_;
+        if (c0_on) {
+            Pending::Term& t = pend.c0;
+            if (nz(t.thr)) op.tw.tslot[RB] = make_thread_table(e, t.thr);
+            if (t.cst != 0 || nz(t.glb)) op.tw.gslot[RB] = (uint16_t)new_gslot(e, t.cst, t.glb);
+            t.clear();
+        }
+        e.ops.push_back(op);
+        return QSV_OK;
     }
 
     void finish_stage_regs(StageCtx& sc, const std::vector<int>& want) {
@@ -1051,8 +1146,9 @@ struct Builder {
                 }
                 case OP_PERMX: o.type = (uint8_t)(DC_PERMX + o.tgt); break;
                 case OP_MPHASE: o.type = DC_MPHASE; break;
-                case OP_DRUN1: o.type = (uint8_t)(DC_DRUN1 + o.dr.abit[0]); break;
-                default: o.type = DC_DRUN; break;
+                case OP_HADD: o.type = (uint8_t)(DC_HADD + o.tgt); break;
+                case OP_W: o.type = DC_W; break;
+                default: o.type = DC_TWID; break;
             }
             sp->ops[i] = o;
         }
@@ -1115,23 +1211,25 @@ struct Builder {
                 }
             }
             finish_stage_regs(sc, want);
-            // budgets: a launch carries at most MAX_OPS ops and MAX_GSLOT per-tile scalars; when either
-            // would overflow, the sweep is closed and the same stage is reopened in the next launch
-            const size_t TAB_PER_RUN = (RB + 1) * TSLOT_LEN + NREG;
-            auto ensure = [&](size_t ops_needed, size_t slots_needed) -> int {
-                if (e.ops.size() + ops_needed > MAX_OPS || e.gslots.size() + slots_needed > MAX_GSLOT ||
-                    e.tab.size() / 2 + TAB_PER_RUN > MAX_TAB) {
-                    int rc = push_sweep(e, false, nullptr);
-                    if (rc) return rc;
-                    emit_stage_op(e, sc);
-                }
-                return QSV_OK;
-            };
-            if (e.ops.size() + 16 > MAX_OPS || e.gslots.size() + 2 * (RB + 1) > MAX_GSLOT || e.tab.size() / 2 + 2 * TAB_PER_RUN > MAX_TAB) {
+            // budgets: a launch carries at most MAX_OPS ops, MAX_GSLOT per-tile scalars and MAX_TAB table entries;
+            // ensure_budget() closes the launch and reopens the same stage in the next one when any would overflow
+            if (e.ops.size() + 16 > MAX_OPS) {
                 int rc = push_sweep(e, false, nullptr);
                 if (rc) return rc;
             }
             emit_stage_op(e, sc);
+            // unnormalised butterflies pay off when the stage has at least two plain Hadamards (the owed
+            // 1/sqrt2 factors are settled by ONE scaling per sweep)
+            auto is_plain_h = [&](const qsv_gate_t& g) {
+                if (g.kind != QSV_DENSE1 || g.ctrl_mask) return false;
+                const double* m = mat(g);
+                const double h = m[0];
+                return std::fabs(h - 0.70710678118654752) < 1e-15 && m[1] == 0 && m[2] == h && m[3] == 0 && m[4] == h && m[5] == 0 &&
+                       m[6] == -h && m[7] == 0;
+            };
+            int n_plain_h = 0;
+            for (size_t q = i; q < j; ++q) n_plain_h += is_plain_h(pg[cur[q]]);
+            const bool hadd_mode = n_plain_h >= 2;
             std::vector<size_t> run;
             const size_t RUN_CHUNK = 64;
             for (size_t q = i; q < j; ++q) {
@@ -1139,33 +1237,54 @@ struct Builder {
                 if (g.kind == QSV_DIAG1) {
                     run.push_back(cur[q]);
                     if (run.size() >= RUN_CHUNK) {
-                        int rc = ensure(2 * RUN_CHUNK + 2, RB + 1);
+                        int rc = emit_diag_run(e, sc, run);
                         if (rc) return rc;
-                        emit_diag_run(e, sc, run);
                         run.clear();
                     }
                     continue;
                 }
-                int rc = ensure(2 * run.size() + 3, RB + 1);
+                int rc = emit_diag_run(e, sc, run);
                 if (rc) return rc;
-                emit_diag_run(e, sc, run);
                 run.clear();
-                SwOp op;
-                memset(&op, 0, sizeof(op));
-                op.type = g.kind == QSV_PERMX ? OP_PERMX : OP_DENSE;
                 const int l = loc_of[g.target_bits[0]];
                 const uint8_t tg = (uint8_t)(std::find(sc.rloc.begin(), sc.rloc.end(), l) - sc.rloc.begin());
-                split_ctrl(g.ctrl_mask, g.ctrl_value, sc, op);
-                op.tgt = tg;
-                if (g.kind != QSV_PERMX) memcpy(op.m, mat(g), 8 * sizeof(double));
+                // a butterfly / swap on register bit tg does not commute with phases deferred on that bit
+                if (pend.bit[tg].any) {
+                    rc = flush_pending(e, sc, 1u << tg, false);
+                    if (rc) return rc;
+                }
+                rc = ensure_budget(e, sc, 1, 0, 0);
+                if (rc) return rc;
+                SwOp op;
+                memset(&op, 0, sizeof(op));
+                if (hadd_mode && is_plain_h(g)) {
+                    op.type = OP_HADD;
+                    op.tgt = tg;
+                    sweep_scale *= mat(g)[0];
+                } else {
+                    op.type = g.kind == QSV_PERMX ? OP_PERMX : OP_DENSE;
+                    split_ctrl(g.ctrl_mask, g.ctrl_value, sc, op);
+                    op.tgt = tg;
+                    if (g.kind != QSV_PERMX) memcpy(op.m, mat(g), 8 * sizeof(double));
+                }
                 e.ops.push_back(op);
                 e.n_gates++;
             }
             {
-                int rc = ensure(2 * run.size() + 2, RB + 1);
+                int rc = emit_diag_run(e, sc, run);
                 if (rc) return rc;
-                emit_diag_run(e, sc, run);
                 run.clear();
+                // stage end: everything deferred must land before the register bits change; the owed scale
+                // rides along if this is the sweep's last stage
+                rc = flush_pending(e, sc, (1u << RB) - 1u, j >= cur.size());
+                if (rc) return rc;
+                if (pend.c0.any) {  // thread-wide factor still pending (not the last stage): apply it now as well
+                    const double keep = sweep_scale;
+                    sweep_scale = 1.0;
+                    rc = flush_pending(e, sc, 0, true);
+                    sweep_scale = keep;
+                    if (rc) return rc;
+                }
             }
             i = j;
         }
@@ -1217,10 +1336,12 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
     }
     // opt in to > 48 KB of dynamic shared memory
     const int smem = (int)(2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2));
-    if (ctx->dtype == QSV_C128)
-        e = cudaFuncSetAttribute(k_sweep<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (k > 11)
+        e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_sweep<double, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                                   : cudaFuncSetAttribute(k_sweep<float, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     else
-        e = cudaFuncSetAttribute(k_sweep<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_sweep<double, 128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                                   : cudaFuncSetAttribute(k_sweep<float, 128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
         delete plan;
         return qsv_fail(ctx, QSV_E_CUDA, "cudaFuncSetAttribute(%d B smem) failed: %s", smem, cudaGetErrorString(e));
@@ -1248,10 +1369,13 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
     const int threads = std::max(32, 1 << (k - RB));
     const uint64_t n_tiles = 1ull << (n - k);
     int occ = 1;
-    if (ctx->dtype == QSV_C128)
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<double>, threads, smem);
-    else
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<float>, threads, smem);
+    if (k > 11) {
+        if (ctx->dtype == QSV_C128) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<double, 256, 1>, threads, smem);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<float, 256, 1>, threads, smem);
+    } else {
+        if (ctx->dtype == QSV_C128) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<double, 128, 3>, threads, smem);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<float, 128, 3>, threads, smem);
+    }
     occ = std::max(occ, 1);
     const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)sm_count * occ);
     for (auto& st : plan->steps) {
@@ -1271,10 +1395,17 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
             QSV_CUDA(ctx, cudaEventCreate(&ev1));
             QSV_CUDA(ctx, cudaEventRecord(ev0, stream));
         }
-        if (ctx->dtype == QSV_C128)
-            k_sweep<double><<<grid, threads, smem, stream>>>((const double2*)cur, (double2*)dstp, plan->d_aux, *st.params);
-        else
-            k_sweep<float><<<grid, threads, smem, stream>>>((const float2*)cur, (float2*)dstp, plan->d_aux, *st.params);
+        if (k > 11) {
+            if (ctx->dtype == QSV_C128)
+                k_sweep<double, 256, 1><<<grid, threads, smem, stream>>>((const double2*)cur, (double2*)dstp, plan->d_aux, *st.params);
+            else
+                k_sweep<float, 256, 1><<<grid, threads, smem, stream>>>((const float2*)cur, (float2*)dstp, plan->d_aux, *st.params);
+        } else {
+            if (ctx->dtype == QSV_C128)
+                k_sweep<double, 128, 3><<<grid, threads, smem, stream>>>((const double2*)cur, (double2*)dstp, plan->d_aux, *st.params);
+            else
+                k_sweep<float, 128, 3><<<grid, threads, smem, stream>>>((const float2*)cur, (float2*)dstp, plan->d_aux, *st.params);
+        }
         QSV_CUDA(ctx, cudaGetLastError());
         static const bool sync_each = getenv("QSV_SYNC") != nullptr;  // debugging aid: surface kernel faults at the launch site
         if (sync_each) QSV_CUDA(ctx, cudaStreamSynchronize(stream));
