@@ -710,6 +710,17 @@ int qsv_permute_bits(qsv_ctx* ctx, const void* in, void* out, int n_bits, const 
     cudaStream_t s = (cudaStream_t)stream;
     QSV_CUDA(ctx, cudaSetDevice(ctx->device));
     const uint64_t n = 1ull << n_bits;
+    {
+        // large states: one gate-free tile sweep with a permuting store (coalesced both ways, HBM speed)
+        const int rc = sweep_permute_run(ctx, in, out, n_bits, perm, s);
+        if (rc == QSV_OK) {
+            ctx->stats.kernel_launches++;
+            ctx->stats.sweeps++;
+            ctx->stats.amp_bytes += 2 * n * amp_size(ctx->dtype);
+            return QSV_OK;
+        }
+        if (rc != QSV_E_UNSUPPORTED) return rc;
+    }
     const unsigned blocks = (unsigned)std::min<uint64_t>((n + 255) / 256, 148 * 32);
     if (ctx->dtype == QSV_C128)
         k_permute_bits<double><<<blocks, 256, 0, s>>>((const double2*)in, (double2*)out, n, bp, fixed_low);

@@ -94,3 +94,4 @@ void sweep_plan_free(SweepPlan* p);
 int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps);
 int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream);
 int sweep_plan_collect_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out);
+int sweep_permute_run(qsv_ctx* ctx, const void* in, void* out, int n_bits, const int* perm, cudaStream_t stream);

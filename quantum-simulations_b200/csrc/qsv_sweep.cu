@@ -380,7 +380,7 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
             switch (type) {
                 DENSE_CASES(DC_DENSE_REAL_NC, op_dense_real, false)
                 DENSE_CASES(DC_DENSE_CPLX_NC, op_dense, false)
-                DENSE_CASES(DC_DENSE_REAL_C, op_dense_real, true)
+                DENSE_CASES(DC_DENSE_REAL_C, op_dense, true)
                 DENSE_CASES(DC_DENSE_CPLX_C, op_dense, true)
                 case DC_PERMX + 0: op_permx<C, 0>(v, op, tpred); break;
                 case DC_PERMX + 1: op_permx<C, 1>(v, op, tpred); break;
@@ -431,22 +431,20 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
                             v[j].y *= sc;
                         }
                     }
-                    const uint32_t na = op.tw_n();
-#pragma unroll
-                    for (int s_ = 0; s_ < RB; ++s_) {
-                        if ((uint32_t)s_ < na) {
-                            double2 e = make_double2(1.0, 0.0);
-                            const uint32_t gsl = op.tw_gslot(s_), tsl = op.tw_tslot(s_);
-                            if (gsl != NONE16) e = smE[gsl];
-                            if (tsl != NONE16) e = cmul(e, cmul(smT[tsl + c_lo], smT[tsl + c_hi]));
-                            switch (op.tw_abit(s_)) {
-                                case 0: mul_bit<C, 0>(v, e); break;
-                                case 1: mul_bit<C, 1>(v, e); break;
-                                case 2: mul_bit<C, 2>(v, e); break;
-                                default: mul_bit<C, 3>(v, e); break;
-                            }
-                        }
-                    }
+                    // slot s_ holds the factor of register bit s_ (abit[s_] == 0xFF: nothing pending on that bit)
+#define TWID_BIT(B)                                                                                      \
+    if (op.tw_abit(B) != 0xFFu) {                                                                        \
+        double2 e = make_double2(1.0, 0.0);                                                              \
+        const uint32_t gsl = op.tw_gslot(B), tsl = op.tw_tslot(B);                                       \
+        if (gsl != NONE16) e = smE[gsl];                                                                 \
+        if (tsl != NONE16) e = cmul(e, cmul(smT[tsl + c_lo], smT[tsl + c_hi]));                          \
+        mul_bit<C, B>(v, e);                                                                             \
+    }
+                    TWID_BIT(0)
+                    TWID_BIT(1)
+                    TWID_BIT(2)
+                    TWID_BIT(3)
+#undef TWID_BIT
                     break;
                 }
                 default:
@@ -997,15 +995,17 @@ struct Builder {
         if (scale_on) sweep_scale = 1.0;
         for (int s_ = 0; s_ <= RB; ++s_) op.tw.tslot[s_] = op.tw.gslot[s_] = NONE16;
         int k_ = 0;
-        for (int ri = 0; ri < RB; ++ri)
+        for (int ri = 0; ri < RB; ++ri) {
+            op.tw.abit[ri] = 0xFF;
             if (((mask >> ri) & 1) && pend.bit[ri].any) {
                 Pending::Term& t = pend.bit[ri];
-                op.tw.abit[k_] = (uint8_t)ri;
-                if (nz(t.thr)) op.tw.tslot[k_] = make_thread_table(e, t.thr);
-                if (t.cst != 0 || nz(t.glb)) op.tw.gslot[k_] = (uint16_t)new_gslot(e, t.cst, t.glb);
+                op.tw.abit[ri] = (uint8_t)ri;
+                if (nz(t.thr)) op.tw.tslot[ri] = make_thread_table(e, t.thr);
+                if (t.cst != 0 || nz(t.glb)) op.tw.gslot[ri] = (uint16_t)new_gslot(e, t.cst, t.glb);
                 t.clear();
                 ++k_;
             }
+        }
         op.tw.n_active = (uint8_t)k_;
         if (c0_on) {
             Pending::Term& t = pend.c0;
@@ -1298,10 +1298,14 @@ struct Builder {
 
 }  // namespace
 
+static int sweep_set_smem_attr(qsv_ctx* ctx, int k);
+
 int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
     const int n = ctx->prog_bits;
     if (n < RB) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "unsupported: fused sweeps need at least %d index bits (have %d)", RB, n);
-    int k = max_tile_bits > 0 ? max_tile_bits : KMAX;
+    // default tile: the whole state when it fits, else 2^11 amplitudes (32 KB): measured best on B200 -- three
+    // double-buffered CTAs per SM hide more latency than one 64 KB-tile CTA
+    int k = max_tile_bits > 0 ? max_tile_bits : (n <= KMAX ? KMAX : 11);
     if (max_tile_bits <= 0 && getenv("QSV_TILE_BITS")) k = atoi(getenv("QSV_TILE_BITS"));  // tuning / debugging aid
     k = std::min(std::min(k, KMAX), n);
     if (k < RB) return qsv_fail(ctx, QSV_E_INVALID, "max_tile_bits must be >= %d", RB);
@@ -1335,16 +1339,12 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
         return qsv_fail(ctx, QSV_E_CUDA, "uploading the sweep tables failed: %s", cudaGetErrorString(e));
     }
     // opt in to > 48 KB of dynamic shared memory
-    const int smem = (int)(2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2));
-    if (k > 11)
-        e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_sweep<double, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                                   : cudaFuncSetAttribute(k_sweep<float, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    else
-        e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_sweep<double, 128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                                   : cudaFuncSetAttribute(k_sweep<float, 128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) {
-        delete plan;
-        return qsv_fail(ctx, QSV_E_CUDA, "cudaFuncSetAttribute(%d B smem) failed: %s", smem, cudaGetErrorString(e));
+    {
+        int rc2 = sweep_set_smem_attr(ctx, k);
+        if (rc2) {
+            delete plan;
+            return rc2;
+        }
     }
     ctx->plan = plan;
     if (out_sweeps) {
@@ -1358,11 +1358,21 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
 // defined in qsv.cu
 int qsv_apply_planned_single(qsv_ctx* ctx, void* state, size_t gate_index, cudaStream_t s);
 
-int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream) {
-    SweepPlan* plan = ctx->plan;
-    const int n = ctx->prog_bits, k = plan->k;
-    void* cur = state;
-    void* other = spare;
+static int sweep_set_smem_attr(qsv_ctx* ctx, int k) {
+    const int smem = (int)(2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2));
+    cudaError_t e;
+    if (k > 11)
+        e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_sweep<double, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                                   : cudaFuncSetAttribute(k_sweep<float, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    else
+        e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_sweep<double, 128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                                   : cudaFuncSetAttribute(k_sweep<float, 128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return qsv_fail(ctx, QSV_E_CUDA, "cudaFuncSetAttribute(%d B smem) failed: %s", smem, cudaGetErrorString(e));
+    return QSV_OK;
+}
+
+static int sweep_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const double* d_aux, const SweepParams& params,
+                        cudaStream_t stream) {
     int sm_count = 148;
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
     const size_t smem = 2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2);
@@ -1378,6 +1388,65 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
     }
     occ = std::max(occ, 1);
     const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)sm_count * occ);
+    if (k > 11) {
+        if (ctx->dtype == QSV_C128)
+            k_sweep<double, 256, 1><<<grid, threads, smem, stream>>>((const double2*)src, (double2*)dst, d_aux, params);
+        else
+            k_sweep<float, 256, 1><<<grid, threads, smem, stream>>>((const float2*)src, (float2*)dst, d_aux, params);
+    } else {
+        if (ctx->dtype == QSV_C128)
+            k_sweep<double, 128, 3><<<grid, threads, smem, stream>>>((const double2*)src, (double2*)dst, d_aux, params);
+        else
+            k_sweep<float, 128, 3><<<grid, threads, smem, stream>>>((const float2*)src, (float2*)dst, d_aux, params);
+    }
+    QSV_CUDA(ctx, cudaGetLastError());
+    return QSV_OK;
+}
+
+// Bit permutation as ONE gate-free tile sweep with a permuting store: out[y] = in[x], bit perm[i] of y = bit i of x.
+// Returns QSV_E_UNSUPPORTED when the state is too small for the tile machinery (caller falls back to k_permute_bits).
+int sweep_permute_run(qsv_ctx* ctx, const void* in, void* out, int n_bits, const int* perm, cudaStream_t stream) {
+    if (n_bits < 9) return QSV_E_UNSUPPORTED;
+    const int k = std::min(n_bits, 11);
+    SweepPlan tmp;
+    tmp.k = k;
+    tmp.aux.resize(2, 0.0);
+    const int saved_bits = ctx->prog_bits;
+    std::vector<qsv_gate_t> saved_gates;
+    saved_gates.swap(ctx->gates);   // the builder scans ctx->gates for SWAPs; give it an empty stream
+    ctx->prog_bits = n_bits;
+    int rc;
+    {
+        Builder b(ctx, &tmp, n_bits, k);
+        std::vector<int> P(perm, perm + n_bits);
+        uint64_t need = b.forced_mask();
+        for (int p = 0; p < n_bits; ++p)
+            if (P[p] < b.c_low) need |= 1ull << p;
+        if (__builtin_popcountll(need) > k) {
+            rc = QSV_E_UNSUPPORTED;
+        } else {
+            b.cur_targets = need;
+            b.choose_tile();
+            Builder::Emit e;
+            rc = b.push_sweep(e, true, &P);
+        }
+    }
+    ctx->gates.swap(saved_gates);
+    ctx->prog_bits = saved_bits;
+    if (rc) return rc;
+    rc = sweep_set_smem_attr(ctx, k);
+    if (rc) return rc;
+    rc = sweep_launch(ctx, n_bits, k, in, out, nullptr, *tmp.steps[0].params, stream);
+    if (rc) return rc;
+    ctx->stats.fused_sweeps++;
+    return QSV_OK;
+}
+
+int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream) {
+    SweepPlan* plan = ctx->plan;
+    const int n = ctx->prog_bits, k = plan->k;
+    void* cur = state;
+    void* other = spare;
     for (auto& st : plan->steps) {
         if (!st.fused) {
             int rc = qsv_apply_planned_single(ctx, cur, st.gate_index, stream);
@@ -1395,18 +1464,10 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
             QSV_CUDA(ctx, cudaEventCreate(&ev1));
             QSV_CUDA(ctx, cudaEventRecord(ev0, stream));
         }
-        if (k > 11) {
-            if (ctx->dtype == QSV_C128)
-                k_sweep<double, 256, 1><<<grid, threads, smem, stream>>>((const double2*)cur, (double2*)dstp, plan->d_aux, *st.params);
-            else
-                k_sweep<float, 256, 1><<<grid, threads, smem, stream>>>((const float2*)cur, (float2*)dstp, plan->d_aux, *st.params);
-        } else {
-            if (ctx->dtype == QSV_C128)
-                k_sweep<double, 128, 3><<<grid, threads, smem, stream>>>((const double2*)cur, (double2*)dstp, plan->d_aux, *st.params);
-            else
-                k_sweep<float, 128, 3><<<grid, threads, smem, stream>>>((const float2*)cur, (float2*)dstp, plan->d_aux, *st.params);
+        {
+            int rc = sweep_launch(ctx, n, k, cur, dstp, plan->d_aux, *st.params, stream);
+            if (rc) return rc;
         }
-        QSV_CUDA(ctx, cudaGetLastError());
         static const bool sync_each = getenv("QSV_SYNC") != nullptr;  // debugging aid: surface kernel faults at the launch site
         if (sync_each) QSV_CUDA(ctx, cudaStreamSynchronize(stream));
         if (ctx->profile) {

@@ -40,18 +40,27 @@ class ShardPlan:
         self.n_loc = n_bits - g_bits
         self.steps = []
         self.where_at = []  # bit-position table valid for each "local" step (logical bit -> physical position)
+        self.relabelled = 0  # source gates absorbed as SWAP relabels
 
     @property
     def n_exchanges(self):
-        return sum(1 for s in self.steps if s[0] == "exchange")
+        return sum(1 for s in self.steps if s[0] in ("exchange", "xall"))
 
 
-def plan_sharded(recs, n_bits, g_bits, restore=True) -> ShardPlan:
+def plan_sharded(recs, n_bits, g_bits, restore=True, relabel_swaps=True) -> ShardPlan:
+    """Cut the gate stream into local segments separated by exchange steps.
+
+    Exchange step ("xall"): the g global bit positions trade places with the top g local positions
+    (global i <-> local n_loc-g+i) -- an all-to-all in which every rank keeps 1/2^g of its shard.
+    Which logical bits get evicted is decided by furthest next use (Belady): before an exchange a
+    local bit permutation (one gate-free tile sweep) parks the g local bits that will not be needed as
+    a non-diagonal target for the longest time in the top local positions.
+    """
     plan = ShardPlan(n_bits, g_bits)
-    n_loc = plan.n_loc
-    if n_loc < 1:
-        raise ValueError("need at least one local bit per rank")
-    L = n_loc - 1
+    n_loc, g = plan.n_loc, g_bits
+    if n_loc < max(1, 2 * g):
+        raise ValueError("need at least 2*log2(world) local bits per rank")
+    top = list(range(n_loc - g, n_loc))
     where = list(range(n_bits))  # logical bit -> physical position
     who = list(range(n_bits))    # physical position -> logical bit
     cur = []
@@ -67,49 +76,150 @@ def plan_sharded(recs, n_bits, g_bits, restore=True) -> ShardPlan:
         who[p1], who[p2] = b2, b1
         where[b1], where[b2] = p2, p1
 
-    def exchange(gpos):
+    def park_at_top(bits):
+        """Local permutation putting the given logical bits (all local) at the top-g local positions."""
+        bits = list(bits)
+        assert len(bits) == g and all(where[b] < n_loc for b in bits)
+        if set(who[p] for p in top) == set(bits):
+            return
         flush()
-        plan.steps.append(("exchange", gpos - n_loc))
-        swap_positions(gpos, L)
-
-    def local_swap(p1, p2):
-        flush()
-        perm = list(range(n_loc))
-        perm[p1], perm[p2] = p2, p1
+        perm = list(range(n_loc))          # perm[i] = destination of the index bit now at position i
+        free_top = [p for p in top if who[p] not in bits]
+        for b in bits:
+            p = where[b]
+            if p in top:
+                continue
+            q = free_top.pop()
+            perm[p], perm[q] = q, p
+            swap_positions(p, q)
         plan.steps.append(("permute", perm))
-        swap_positions(p1, p2)
 
+    def xall():
+        flush()
+        plan.steps.append(("xall",))
+        for i in range(g):
+            swap_positions(n_loc + i, n_loc - g + i)
+
+    def cnot(r):
+        if int(r["kind"]) != PERMX or int(r["n_targets"]) != 1:
+            return None
+        cm = int(r["ctrl_mask"])
+        if bin(cm).count("1") != 1 or int(r["ctrl_value"]) != cm:
+            return None
+        return cm.bit_length() - 1, int(r["target_bits"][0])
+
+    # classify records once: SWAP triples (relabels) and the non-diagonal target uses of every logical bit
+    n_recs = len(recs)
+    swap_at = {}
+    i = 0
+    while relabel_swaps and i + 2 < n_recs:
+        c0, c1, c2 = cnot(recs[i]), cnot(recs[i + 1]), cnot(recs[i + 2])
+        if c0 and c1 and c2 and c1 == (c0[1], c0[0]) and c2 == c0:
+            swap_at[i] = c0
+            i += 3
+        else:
+            i += 1
+    uses = [[] for _ in range(n_bits)]     # per logical bit: record indexes where it is a non-diagonal target
+    label = list(range(n_bits))            # relabel-aware: which CURRENT logical name a future use refers to
+    # (uses are recorded against the logical bit named in the record; relabels rename data, handled below)
+    skip = set()
+    for i0, (a, b) in swap_at.items():
+        skip.update((i0, i0 + 1, i0 + 2))
     for i, r in enumerate(recs):
+        if i in skip or int(r["kind"]) in (DIAG1, ROWS2):
+            continue
+        for tb in r["target_bits"][:int(r["n_targets"])]:
+            uses[int(tb)].append(i)
+
+    import bisect
+
+    def next_use(b, i):
+        """Index of the next record (>= i) that needs logical bit b as a non-diagonal target.  SWAP relabels
+        between now and then rename the data, so follow them: the data now called b is called tau(b) later."""
+        name = b
+        best = None
+        # walk forward through relabels in order; between relabels look up uses of the current name
+        pos_i = i
+        for s_i in sorted(k_ for k_ in swap_at if k_ >= i):
+            lst = uses[name]
+            j = bisect.bisect_left(lst, pos_i)
+            if j < len(lst) and lst[j] < s_i:
+                return lst[j]
+            a, b2 = swap_at[s_i]
+            if name == a:
+                name = b2
+            elif name == b2:
+                name = a
+            pos_i = s_i
+        lst = uses[name]
+        j = bisect.bisect_left(lst, pos_i)
+        return lst[j] if j < len(lst) else n_recs + 1
+
+    i = 0
+    while i < n_recs:
+        r = recs[i]
+        if i in swap_at:
+            flush()  # gates already collected were mapped with the table as it was
+            a, b = swap_at[i]
+            swap_positions(where[a], where[b])
+            plan.relabelled += 3
+            i += 3
+            continue
         kind = int(r["kind"])
         if kind == ROWS2:
             raise NotImplementedError("row (two-level) records are column-sharded, not state-sharded")
         t = int(r["n_targets"])
         tbits = [int(b) for b in r["target_bits"][:t]]
-        if kind != DIAG1:
-            pinned = []
-            for tb in tbits:
-                if where[tb] >= n_loc:
-                    if who[L] in pinned:  # the top local bit already holds a target of this gate: move it aside
-                        free = next(p for p in range(L - 1, -1, -1) if who[p] not in tbits)
-                        local_swap(L, free)
-                    exchange(where[tb])
-                pinned.append(tb)
+        if kind != DIAG1 and any(where[tb] >= n_loc for tb in tbits):
+            # evict the g local bits whose next non-diagonal use is furthest away (never the gate's own targets)
+            cand = [who[p] for p in range(n_loc) if who[p] not in tbits]
+            cand.sort(key=lambda b: -next_use(b, i))
+            park_at_top(cand[:g])
+            xall()
+            assert all(where[tb] < n_loc for tb in tbits)
         cur.append(i)
+        i += 1
     flush()
     if restore:
-        # bring every logical bit back to its canonical position: globals first (each needs its bit at L), then locals
-        for gpos in range(n_bits - 1, n_loc - 1, -1):
-            if who[gpos] == gpos:
-                continue
-            p = where[gpos]          # where the wanted logical bit sits now
-            if p >= n_loc:
-                exchange(p)          # bring it to L
-            elif p != L:
-                local_swap(p, L)
-            exchange(gpos)
+        want_global = list(range(n_loc, n_bits))
+        if any(who[p] != p for p in want_global):
+            if any(where[b] >= n_loc for b in want_global):
+                # some of the bits that belong on global positions are global already (maybe misplaced): bring
+                # everything local first, evicting bits that do not belong up there
+                victims = [who[p] for p in range(n_loc) if who[p] not in want_global][:g]
+                park_at_top(victims)
+                xall()
+            park_in_order = [n_loc + i for i in range(g)]
+            # top local position n_loc-g+i must hold logical bit n_loc+i before the exchange
+            if [who[p] for p in top] != park_in_order:
+                flush()
+                perm = list(range(n_loc))
+                # build the permutation position by position
+                dest = {}
+                for i_, b in enumerate(park_in_order):
+                    dest[where[b]] = top[i_]
+                taken = set(dest.values())
+                free = [p for p in range(n_loc) if p not in taken]
+                movers = [p for p in range(n_loc) if p not in dest]
+                # keep everything else in place when possible
+                remaining = [p for p in movers if p in free]
+                for p in remaining:
+                    dest[p] = p
+                    free.remove(p)
+                for p in movers:
+                    if p not in dest:
+                        dest[p] = free.pop()
+                perm = [dest[p] for p in range(n_loc)]
+                newwho = list(who)
+                for p in range(n_loc):
+                    newwho[perm[p]] = who[p]
+                for p in range(n_loc):
+                    who[p] = newwho[p]
+                    where[who[p]] = p
+                plan.steps.append(("permute", perm))
+            xall()
         if who[:n_loc] != list(range(n_loc)):
             flush()
-            # perm[i] = destination position of the index bit currently at position i (= the logical bit it holds)
             plan.steps.append(("permute", [who[p] for p in range(n_loc)]))
             for p in range(n_loc):
                 who[p] = p
@@ -199,6 +309,36 @@ class TorchExchanger:
         self.bytes_sent += send.numel() * send.element_size()
         return state
 
+    def exchange_all(self, state, spare):
+        if self.dist.get_backend() == "gloo":
+            # gloo has no all_to_all: emulate with pairwise chunk swaps (CPU tests only)
+            import torch
+            w = self.world
+            inp = torch.view_as_real(state).view(w, -1)
+            out = torch.view_as_real(spare).view(w, -1)
+            out[self.rank].copy_(inp[self.rank])
+            ops = []
+            for peer in range(w):
+                if peer != self.rank:
+                    ops.append(self.dist.P2POp(self.dist.isend, inp[peer], peer))
+                    ops.append(self.dist.P2POp(self.dist.irecv, out[peer], peer))
+            for req in self.dist.batch_isend_irecv(ops):
+                req.wait()
+            res = (spare, state)
+        else:
+            res = _exchange_all(self.dist, state, spare, self.world)
+        self.bytes_sent += state.numel() * state.element_size() * (self.world - 1) // self.world
+        return res
+
+
+def _exchange_all(dist, state, spare, world):
+    """All global bits <-> the top local bits: chunk c of this rank goes to rank c (NCCL/gloo all-to-all)."""
+    import torch
+    inp = torch.view_as_real(state).view(world, -1)
+    out = torch.view_as_real(spare).view(world, -1)
+    dist.all_to_all_single(out, inp)
+    return spare, state
+
 
 class GpuExecutor:
     """Runs local segments on the CUDA engine; one libqsv context (with its fused plan) per segment."""
@@ -283,6 +423,8 @@ class ShardedCircuit:
                 li += 1
             elif s[0] == "exchange":
                 state = self.exchanger.exchange(state, spare, s[1])
+            elif s[0] == "xall":
+                state, spare = self.exchanger.exchange_all(state, spare)
             else:
                 state, spare = self.executor.permute(state, spare, self.n_loc, s[1])
         return state, spare

@@ -48,7 +48,7 @@ class FakeWorld:
     def __init__(self, shards):
         self.shards = shards
 
-    def exchange_all(self, gbit):
+    def exchange_pair(self, gbit):
         done = set()
         for r in range(len(self.shards)):
             p = r ^ (1 << gbit)
@@ -60,6 +60,15 @@ class FakeWorld:
             self.shards[lo][half:] = self.shards[hi][:half]
             self.shards[hi][:half] = tmp
             done.update((r, p))
+
+    def exchange_all(self):
+        w = len(self.shards)
+        chunk = self.shards[0].size // w
+        new = [np.empty_like(s) for s in self.shards]
+        for r in range(w):
+            for c in range(w):
+                new[r][c * chunk:(c + 1) * chunk] = self.shards[c][r * chunk:(r + 1) * chunk]
+        self.shards[:] = new
 
 
 def run_emulated(recs, pool, n, world, x):
@@ -73,6 +82,9 @@ def run_emulated(recs, pool, n, world, x):
         def exchange(self, state, spare, gbit):
             return state
 
+        def exchange_all(self, state, spare):
+            return state, spare
+
     circs = [ShardedCircuit(recs, pool, n, r, world, OracleExecutor(), NullEx()) for r in range(world)]
     plan = circs[0].plan
     assert all(c.plan.steps == plan.steps for c in circs), "plan must be rank independent"
@@ -83,7 +95,9 @@ def run_emulated(recs, pool, n, world, x):
                 fw.shards[r], spares[r] = circs[r].executor.run_segment(li, fw.shards[r], spares[r])
             li += 1
         elif s[0] == "exchange":
-            fw.exchange_all(s[1])
+            fw.exchange_pair(s[1])
+        elif s[0] == "xall":
+            fw.exchange_all()
         else:
             for r in range(world):
                 fw.shards[r], spares[r] = circs[r].executor.permute(fw.shards[r], spares[r], n_loc, s[1])
