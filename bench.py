@@ -106,6 +106,15 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def ncu_traffic(n):
+    """DRAM bytes per k_sweep launch from the committed `ncu --set full` capture (profiles/), or None."""
+    p = os.path.join(ROOT, "profiles", "ncu_k_sweep_traffic.json")
+    try:
+        return json.load(open(p)).get(f"qft{n}", {}).get("dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -270,7 +279,8 @@ def run_single(args):
                        "sweeps_per_step": n_sweeps, "l2": "state (16 B x 2^n) is far larger than the 126 MB L2"},
             "amp_GBps": amp_gbps, "hbm_frac_of_measured": amp_gbps / peak,
             "roofline": {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                         "frac": achieved / peak, "bytes_per_launch": per_launch_bytes, "avg_launch_ms": avg_ms, "traffic": None},
+                         "frac": achieved / peak, "bytes_per_launch": per_launch_bytes, "avg_launch_ms": avg_ms,
+                         "traffic": ncu_traffic(n) if fused else None},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "sweep_ms_first_step": sweep_ms}
     print(json.dumps(line))
 

@@ -326,3 +326,21 @@ def test_large_state_properties():
         assert abs(complex(back[0]) - 1.0) < 1e-10
         assert float(back[1:].abs().max()) < 1e-10
         del spare
+
+
+def test_complex64_fused_path():
+    """The fused tile sweep in complex64 (float2 amplitudes, 8-byte cp.async): 1e-5 against the complex128 oracle,
+    bit-exact for a permutation stream."""
+    from quantum_simulations_b200.utils.mgen import qft_program
+    n = 13
+    prog = qft_program(n)
+    x = np.stack([random_state(1 << n) for _ in range(2)], axis=1)
+    eng = get_engine(np.complex64)
+    eng.reset_stats()
+    got = apply_circuit(prog, x.astype(np.complex64), dtype=np.complex64, fuse=True)
+    assert eng.stats()["fused_sweeps"] > 0 and got.dtype == np.complex64
+    assert np.abs(got - orc.qft_reference(x)).max() < TOL64
+    d = load("streams")
+    leaves = unpack_gates(d, "cyc16")
+    assert np.array_equal(reconstruct_unitary(leaves[::-1], drop_ancilla=True, dtype=np.complex64, fuse=True),
+                          d["cyc16_value"].astype(np.complex64))
