@@ -13,6 +13,7 @@
 // All are HBM-bound streaming kernels: one 128-bit load + one 128-bit store per touched
 // complex128 amplitude, 4 independent pairs per thread in flight.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "qsv_common.cuh"
 
@@ -486,6 +487,7 @@ void qsv_destroy(qsv_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->plan) sweep_plan_free(ctx->plan);
+    if (ctx->rows_plan) rowslab_free(ctx->rows_plan);
     if (ctx->d_mat) cudaFree(ctx->d_mat);
     if (ctx->d_red) cudaFree(ctx->d_red);
     if (ctx->d_pool) cudaFree(ctx->d_pool);
@@ -588,6 +590,7 @@ int qsv_upload_program(qsv_ctx* ctx, int n_bits, int batch_bits, const qsv_gate_
     }
     QSV_CUDA(ctx, cudaSetDevice(ctx->device));
     if (ctx->plan) { sweep_plan_free(ctx->plan); ctx->plan = nullptr; }
+    if (ctx->rows_plan) { rowslab_free(ctx->rows_plan); ctx->rows_plan = nullptr; }
     if (ctx->d_pool) { cudaFree(ctx->d_pool); ctx->d_pool = nullptr; }
     ctx->gates.assign(gates, gates + n_gates);
     ctx->pool.assign(pool, pool + 2 * pool_elems);
@@ -605,6 +608,20 @@ int qsv_fuse(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
     if (!ctx) return QSV_E_INVALID;
     if (!ctx->has_program) return qsv_fail(ctx, QSV_E_NOPROGRAM, "qsv_fuse before qsv_upload_program");
     QSV_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ctx->rows_plan) { rowslab_free(ctx->rows_plan); ctx->rows_plan = nullptr; }
+    {
+        // streams made only of two-level / fully controlled gates: column-slab kernel, one pass for the whole program
+        static const bool no_rows = getenv("QSV_NO_ROWSLAB") != nullptr;  // debugging aid
+        RowSlabPlan* rp = nullptr;
+        const int rc = no_rows ? QSV_E_UNSUPPORTED : rowslab_build(ctx, &rp);
+        if (rc == QSV_OK) {
+            if (ctx->plan) { sweep_plan_free(ctx->plan); ctx->plan = nullptr; }
+            ctx->rows_plan = rp;
+            if (out_sweeps) *out_sweeps = 1;
+            return QSV_OK;
+        }
+        if (rc != QSV_E_UNSUPPORTED) return rc;
+    }
     return sweep_plan_build(ctx, max_tile_bits, out_sweeps);
 }
 
@@ -627,6 +644,7 @@ int qsv_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, void* 
     cudaStream_t s = (cudaStream_t)stream;
     QSV_CUDA(ctx, cudaSetDevice(ctx->device));
     if (result_in_spare) *result_in_spare = 0;
+    if (ctx->rows_plan) return rowslab_run(ctx, ctx->rows_plan, state, s);
     if (ctx->plan) return sweep_plan_run(ctx, state, spare, result_in_spare, s);
     for (size_t i = 0; i < ctx->gates.size(); ++i) {
         const qsv_gate_t& g = ctx->gates[i];

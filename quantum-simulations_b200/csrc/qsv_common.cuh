@@ -55,7 +55,8 @@ __host__ __device__ __forceinline__ uint64_t bit_expand(uint64_t i, const BitIns
 struct Mat2 { double m[8]; };  // row-major (re,im) x 4
 
 // ---- fused-plan types (qsv_sweep.cu) -----------------------------------------------------------
-struct SweepPlan;  // opaque here
+struct SweepPlan;    // opaque here (qsv_sweep.cu)
+struct RowSlabPlan;  // opaque here (qsv_rows.cu)
 
 struct qsv_ctx {
     int device = 0;
@@ -75,6 +76,7 @@ struct qsv_ctx {
     double* d_pool = nullptr;      // device copy
     // fused plan
     SweepPlan* plan = nullptr;
+    RowSlabPlan* rows_plan = nullptr;  // set instead of `plan` when the whole program is row-pair operations
     bool profile = false;          // record CUDA events around every fused sweep
 };
 
@@ -94,4 +96,8 @@ void sweep_plan_free(SweepPlan* p);
 int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps);
 int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream);
 int sweep_plan_collect_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out);
+// implemented in qsv_rows.cu
+void rowslab_free(RowSlabPlan* p);
+int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out);
+int rowslab_run(qsv_ctx* ctx, RowSlabPlan* plan, void* state, cudaStream_t stream);
 int sweep_permute_run(qsv_ctx* ctx, const void* in, void* out, int n_bits, const int* perm, cudaStream_t stream);

@@ -344,3 +344,55 @@ def test_complex64_fused_path():
     leaves = unpack_gates(d, "cyc16")
     assert np.array_equal(reconstruct_unitary(leaves[::-1], drop_ancilla=True, dtype=np.complex64, fuse=True),
                           d["cyc16_value"].astype(np.complex64))
+
+
+@pytest.mark.parametrize("N", [8, 32, 128])
+def test_config4_fully_controlled_stream_rowslab(N):
+    """BASELINE config 4 at reduced size: random N x N unitary -> SINGLET stream (every gate fully controlled)
+    -> full unitary reconstruction on N basis columns.  The fusion pass folds the stream into row-pair ops and
+    runs the column-slab kernel: one pass over the state for the whole program."""
+    from quantum_simulations_b200.utils.producers import singlet_records, two_level_records, two_level_stream
+    np.random.seed(N)
+    u = random_unitary(N)
+    stream = two_level_stream(u)
+    n = N.bit_length() - 1
+    recs, pool = singlet_records(stream, n, batch_bits=n)
+    eng = get_engine()
+    for fuse in (True, False):
+        st = eng.empty(N * N)
+        eng.init_basis_columns(st, 2 * n, n, 0, 0)
+        eng.upload_records(recs, pool, 2 * n, n)
+        eng.reset_stats()
+        if fuse:
+            assert eng.fuse() == 1                    # the whole program became ONE slab pass
+        if N > 32 and not fuse:
+            continue                                  # 49k single launches: skip the slow leg at N = 128
+        res = eng.run(st, None)
+        stt = eng.stats()
+        assert stt["gates_applied"] == len(recs)
+        if fuse:
+            assert stt["kernel_launches"] == 1
+        assert np.abs(res.view(N, N).cpu().numpy() - u).max() < TOL128
+    # the same stream as two-level (ROWS2) records
+    r2, p2 = two_level_records(stream)
+    st = eng.empty(N * N)
+    eng.init_basis_columns(st, 2 * n, n, 0, 0)
+    eng.upload_records(r2, p2, 2 * n, n)
+    assert eng.fuse() == 1
+    assert np.abs(eng.run(st, None).view(N, N).cpu().numpy() - u).max() < TOL128
+
+
+def test_rowslab_permutation_streams_bit_exact():
+    """Cyclic-permutation SINGLET streams (only fully controlled X): folded into row relabels + exchanges, bit-exact."""
+    d = load("streams")
+    for name in ("cfg2s", "cyc16"):
+        leaves = unpack_gates(d, name)
+        prog = flatten(leaves[::-1])
+        n = prog.n_qubits
+        eng = get_engine()
+        st = eng.empty(1 << (2 * n))
+        eng.init_basis_columns(st, 2 * n, n, 0, 0)
+        eng.upload(prog, n)
+        assert eng.fuse() == 1
+        res = eng.run(st, None).view(1 << n, 1 << n).cpu().numpy()
+        assert np.array_equal(res, d[f"{name}_value"])

@@ -236,3 +236,37 @@ print("ok", len(circ), [repr(q) for q in circ.all_qubits()])
 ''' % ROOT
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+
+
+def test_fast_two_level_producer_matches_reference():
+    """O(N^3) Givens producer == the reference's mat2l_decompose output (tests/golden/two_level.npz)."""
+    from quantum_simulations_b200.utils.producers import two_level_stream
+    d = load("two_level")
+    for name in ("d8", "d3", "d6"):
+        stream = two_level_stream(d[f"{name}_input"])
+        assert [(i, j) for i, j, _ in stream] == [tuple(c) for c in d[f"{name}_core"].tolist()]
+        for (_, _, c), ref in zip(stream, d[f"{name}_mat"]):
+            assert np.abs(c - ref).max() < 1e-12
+
+
+def test_fast_singlet_producer_reproduces_the_unitary():
+    """SINGLET records written directly (Gray chains) rebuild the input unitary through the oracle."""
+    from quantum_simulations_b200.utils.producers import singlet_records, two_level_records, two_level_stream
+    d = load("streams")
+    u = d["r32_input"]
+    stream = two_level_stream(u)
+    n = 5
+    recs, pool = singlet_records(stream, n, batch_bits=n)
+    assert set(recs["kind"].tolist()) <= {_lib.PERMX, _lib.DENSE1, _lib.DIAG1}
+    full = ((1 << n) - 1) << n
+    assert all((int(r["ctrl_mask"]) | (1 << int(r["target_bits"][0]))) == full for r in recs)   # every gate fully controlled
+    st = np.eye(32, dtype=np.complex128).reshape(-1).copy()
+    orc.run_records(recs, pool, st, 2 * n)
+    assert np.abs(st.reshape(32, 32) - u).max() < 1e-12
+    # the two-level (ROWS2) form of the same stream
+    r2, p2 = two_level_records(stream)
+    st2 = np.eye(32, dtype=np.complex128)
+    for r in r2:
+        off = int(r["matrix_offset"])
+        orc.apply_two_level(st2, (int(r["row0"]), int(r["row1"])), p2[off:off + 4].reshape(2, 2))
+    assert np.abs(st2 - u).max() < 1e-12
