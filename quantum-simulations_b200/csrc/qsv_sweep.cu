@@ -57,7 +57,6 @@ enum : uint8_t {
     DC_W = 26,               // register-register phase table: v[j] *= W[j]
     DC_TWID = 27,            // deferred per-register-bit phases (thread / tile dependent) + thread-wide factor + real scale
 };
-enum : uint8_t { FLAG_REAL = 1 };
 #define NONE16 0xFFFFu
 #define NONE32 0xFFFFFFFFu
 
@@ -274,7 +273,9 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 
 // Two instantiations: <256, 1> for 64 KB tiles (k = 12, one CTA per SM) and <128, 3> for smaller tiles
 // (register cap 168 so that three double-buffered 32 KB-tile CTAs share an SM).
-template <typename R, int MAXT, int MINB>
+// LEAN = the op set of Hadamard/phase circuits only (stage, uncontrolled dense, unnormalised butterfly, phase tables):
+// a smaller kernel image for the common case; the full image adds controlled dense gates, swaps and masked phases.
+template <typename R, int MAXT, int MINB, bool LEAN>
 __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>::type* __restrict__ src,
                                                   typename cplx_of<R>::type* __restrict__ dst,
                                                   const double* __restrict__ aux,
@@ -380,18 +381,22 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
             switch (type) {
                 DENSE_CASES(DC_DENSE_REAL_NC, op_dense_real, false)
                 DENSE_CASES(DC_DENSE_CPLX_NC, op_dense, false)
-                DENSE_CASES(DC_DENSE_REAL_C, op_dense, true)
-                DENSE_CASES(DC_DENSE_CPLX_C, op_dense, true)
-                case DC_PERMX + 0: op_permx<C, 0>(v, op, tpred); break;
-                case DC_PERMX + 1: op_permx<C, 1>(v, op, tpred); break;
-                case DC_PERMX + 2: op_permx<C, 2>(v, op, tpred); break;
-                case DC_PERMX + 3: op_permx<C, 3>(v, op, tpred); break;
+                case DC_DENSE_CPLX_C + 0: if constexpr (!LEAN) op_dense<C, true, 0>(v, op, tpred); break;
+                case DC_DENSE_CPLX_C + 1: if constexpr (!LEAN) op_dense<C, true, 1>(v, op, tpred); break;
+                case DC_DENSE_CPLX_C + 2: if constexpr (!LEAN) op_dense<C, true, 2>(v, op, tpred); break;
+                case DC_DENSE_CPLX_C + 3: if constexpr (!LEAN) op_dense<C, true, 3>(v, op, tpred); break;
+                case DC_PERMX + 0: if constexpr (!LEAN) op_permx<C, 0>(v, op, tpred); break;
+                case DC_PERMX + 1: if constexpr (!LEAN) op_permx<C, 1>(v, op, tpred); break;
+                case DC_PERMX + 2: if constexpr (!LEAN) op_permx<C, 2>(v, op, tpred); break;
+                case DC_PERMX + 3: if constexpr (!LEAN) op_permx<C, 3>(v, op, tpred); break;
                 case DC_MPHASE: {
-                    const C d = cmake<C, R>((R)op.m(0), (R)op.m(1));
-                    const uint32_t rm = op.rmask(), rv = op.rval();
+                    if constexpr (!LEAN) {
+                        const C d = cmake<C, R>((R)op.m(0), (R)op.m(1));
+                        const uint32_t rm = op.rmask(), rv = op.rval();
 #pragma unroll
-                    for (int j = 0; j < NREG; ++j)
-                        if (((j & rm) == rv) && tpred) v[j] = cmul(v[j], d);
+                        for (int j = 0; j < NREG; ++j)
+                            if (((j & rm) == rv) && tpred) v[j] = cmul(v[j], d);
+                    }
                     break;
                 }
                 case DC_HADD + 0: op_hadd<C, 0>(v); break;
@@ -487,6 +492,7 @@ struct PlanStep {
     size_t gate_index;      // !fused: index into ctx->gates
     SweepParams* params;    // fused (host copy)
     bool out_of_place;
+    bool lean;              // every op is in the lean kernel's set
     uint64_t n_gates;       // source gates carried
 };
 
@@ -594,12 +600,6 @@ struct Builder {
                 i += 2;
             }
         }
-    }
-
-    bool identity_layout() const {
-        for (int b = 0; b < n; ++b)
-            if (pos[b] != b) return false;
-        return true;
     }
 
     // rewrite a source gate to the physical positions its bits occupy right now
@@ -1134,6 +1134,7 @@ struct Builder {
             D.in_glob = make_segmap64(gin);
             D.out_glob = make_segmap64(gout);
         }
+        bool all_lean = true;
         for (size_t i = 0; i < e.ops.size(); ++i) {
             SwOp o = e.ops[i];
             const bool ctrl = o.rmask || o.lmask;
@@ -1141,7 +1142,7 @@ struct Builder {
                 case OP_STAGE: o.type = DC_STAGE; break;
                 case OP_DENSE: {
                     const bool real = o.m[1] == 0.0 && o.m[3] == 0.0 && o.m[5] == 0.0 && o.m[7] == 0.0;
-                    o.type = (uint8_t)((real ? (ctrl ? DC_DENSE_REAL_C : DC_DENSE_REAL_NC) : (ctrl ? DC_DENSE_CPLX_C : DC_DENSE_CPLX_NC)) + o.tgt);
+                    o.type = (uint8_t)((ctrl ? DC_DENSE_CPLX_C : (real ? DC_DENSE_REAL_NC : DC_DENSE_CPLX_NC)) + o.tgt);
                     break;
                 }
                 case OP_PERMX: o.type = (uint8_t)(DC_PERMX + o.tgt); break;
@@ -1151,11 +1152,14 @@ struct Builder {
                 default: o.type = DC_TWID; break;
             }
             sp->ops[i] = o;
+            const uint8_t c_ = o.type;
+            if ((c_ >= DC_DENSE_REAL_C && c_ < DC_HADD) || c_ == DC_MPHASE) all_lean = false;
         }
         PlanStep s{};
         s.fused = true;
         s.params = sp;
         s.out_of_place = out_of_place;
+        s.lean = all_lean;
         s.n_gates = e.n_gates;
         plan->steps.push_back(s);
         e = Emit();
@@ -1358,48 +1362,52 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
 // defined in qsv.cu
 int qsv_apply_planned_single(qsv_ctx* ctx, void* state, size_t gate_index, cudaStream_t s);
 
+template <typename R, int MAXT, int MINB, bool LEAN>
+static cudaError_t sweep_image_launch(bool set_attr_only, int* occ_out, unsigned grid, int threads, size_t smem, cudaStream_t stream,
+                                      const void* src, void* dst, const double* d_aux, const SweepParams* params) {
+    typedef typename cplx_of<R>::type C;
+    auto kern = k_sweep<R, MAXT, MINB, LEAN>;
+    if (set_attr_only) return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (occ_out) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ_out, kern, threads, smem);
+    kern<<<grid, threads, smem, stream>>>((const C*)src, (C*)dst, d_aux, *params);
+    return cudaGetLastError();
+}
+
+// picks the kernel image for (dtype, tile size, lean) and either sets its smem attribute, queries occupancy or launches it
+static cudaError_t sweep_image(qsv_ctx* ctx, int k, bool lean, bool set_attr_only, int* occ_out, unsigned grid, int threads, size_t smem,
+                               cudaStream_t stream, const void* src, void* dst, const double* d_aux, const SweepParams* params) {
+#define IMG(R, MAXT, MINB, LEAN) sweep_image_launch<R, MAXT, MINB, LEAN>(set_attr_only, occ_out, grid, threads, smem, stream, src, dst, d_aux, params)
+    const bool dbl = ctx->dtype == QSV_C128;
+    if (k > 11) {
+        if (dbl) return lean ? IMG(double, 256, 1, true) : IMG(double, 256, 1, false);
+        return lean ? IMG(float, 256, 1, true) : IMG(float, 256, 1, false);
+    }
+    if (dbl) return lean ? IMG(double, 128, 3, true) : IMG(double, 128, 3, false);
+    return lean ? IMG(float, 128, 3, true) : IMG(float, 128, 3, false);
+#undef IMG
+}
+
 static int sweep_set_smem_attr(qsv_ctx* ctx, int k) {
-    const int smem = (int)(2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2));
-    cudaError_t e;
-    if (k > 11)
-        e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_sweep<double, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                                   : cudaFuncSetAttribute(k_sweep<float, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    else
-        e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_sweep<double, 128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                                   : cudaFuncSetAttribute(k_sweep<float, 128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return qsv_fail(ctx, QSV_E_CUDA, "cudaFuncSetAttribute(%d B smem) failed: %s", smem, cudaGetErrorString(e));
+    const size_t smem = 2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2);
+    for (int lean = 0; lean < 2; ++lean) {
+        cudaError_t e = sweep_image(ctx, k, lean != 0, true, nullptr, 0, 0, smem, nullptr, nullptr, nullptr, nullptr, nullptr);
+        if (e != cudaSuccess) return qsv_fail(ctx, QSV_E_CUDA, "cudaFuncSetAttribute(%zu B smem) failed: %s", smem, cudaGetErrorString(e));
+    }
     return QSV_OK;
 }
 
 static int sweep_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const double* d_aux, const SweepParams& params,
-                        cudaStream_t stream) {
+                        cudaStream_t stream, bool lean = false) {
     int sm_count = 148;
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
     const size_t smem = 2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2);
     const int threads = std::max(32, 1 << (k - RB));
     const uint64_t n_tiles = 1ull << (n - k);
     int occ = 1;
-    if (k > 11) {
-        if (ctx->dtype == QSV_C128) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<double, 256, 1>, threads, smem);
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<float, 256, 1>, threads, smem);
-    } else {
-        if (ctx->dtype == QSV_C128) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<double, 128, 3>, threads, smem);
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_sweep<float, 128, 3>, threads, smem);
-    }
+    sweep_image(ctx, k, lean, false, &occ, 0, threads, smem, stream, nullptr, nullptr, nullptr, nullptr);
     occ = std::max(occ, 1);
     const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)sm_count * occ);
-    if (k > 11) {
-        if (ctx->dtype == QSV_C128)
-            k_sweep<double, 256, 1><<<grid, threads, smem, stream>>>((const double2*)src, (double2*)dst, d_aux, params);
-        else
-            k_sweep<float, 256, 1><<<grid, threads, smem, stream>>>((const float2*)src, (float2*)dst, d_aux, params);
-    } else {
-        if (ctx->dtype == QSV_C128)
-            k_sweep<double, 128, 3><<<grid, threads, smem, stream>>>((const double2*)src, (double2*)dst, d_aux, params);
-        else
-            k_sweep<float, 128, 3><<<grid, threads, smem, stream>>>((const float2*)src, (float2*)dst, d_aux, params);
-    }
-    QSV_CUDA(ctx, cudaGetLastError());
+    QSV_CUDA(ctx, sweep_image(ctx, k, lean, false, nullptr, grid, threads, smem, stream, src, dst, d_aux, &params));
     return QSV_OK;
 }
 
@@ -1465,7 +1473,7 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
             QSV_CUDA(ctx, cudaEventRecord(ev0, stream));
         }
         {
-            int rc = sweep_launch(ctx, n, k, cur, dstp, plan->d_aux, *st.params, stream);
+            int rc = sweep_launch(ctx, n, k, cur, dstp, plan->d_aux, *st.params, stream, st.lean);
             if (rc) return rc;
         }
         static const bool sync_each = getenv("QSV_SYNC") != nullptr;  // debugging aid: surface kernel faults at the launch site

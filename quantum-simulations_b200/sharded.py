@@ -21,11 +21,10 @@ There is no reference counterpart: the reference is single-process numpy (SURVEY
 import json
 import os
 import sys
-import time
 
 import numpy as np
 
-from ._lib import DENSEK, DIAG1, GATE_DTYPE, PERMX, ROWS2
+from ._lib import DIAG1, GATE_DTYPE, PERMX, ROWS2
 
 
 # ---------------------------------------------------------------------------------------------
@@ -492,6 +491,32 @@ def bench_main(args):
     # norm check (unitarity) as a cheap correctness guard of the whole sharded run
     nrm = torch.linalg.vector_norm(state) ** 2
     dist.all_reduce(nrm)
+    # end to end through host buffers: every rank uploads its shard from pinned memory, applies the circuit and
+    # downloads the result, every step; max over ranks
+    e2e = None
+    if args.e2e_steps > 0:
+        host = torch.empty(amps, dtype=torch.complex128, pin_memory=True)
+        host.copy_(state)
+        torch.cuda.synchronize()
+        dist.barrier()
+        t_e2e = []
+        for i in range(args.e2e_steps + 1):
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            dist.barrier()
+            a0.record()
+            state.copy_(host, non_blocking=True)
+            state, spare = circ.apply(state, spare)
+            host.copy_(state, non_blocking=True)
+            a1.record()
+            torch.cuda.synchronize()
+            tt = torch.tensor([a0.elapsed_time(a1)], device=dev, dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            if i > 0:
+                t_e2e.append(float(tt.item()))
+        e2e_ms = float(np.mean(t_e2e))
+        e2e = {"value": circ.n_gates / (e2e_ms / 1e3), "unit": "gates/s", "h2d_bytes_per_step": amps * 16 * world,
+               "d2h_bytes_per_step": amps * 16 * world, "ms_per_step": e2e_ms, "steps": args.e2e_steps}
+        del host
     if rank == 0:
         sec = ms / 1e3
         peak, peak_src = B.measured_peak()
@@ -508,7 +533,7 @@ def bench_main(args):
                              "achieved": amp_gbps / world, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                              "frac": amp_gbps / world / peak, "traffic": None},
                 "nvlink": {"bytes_sent_per_rank_per_step": float(tot[2]) / world / args.steps, "exchanges_per_step": n_ex},
-                "cpu_baseline": None, "e2e": None, "gpu_launches": int(tot[1]), "clocks": clocks,
+                "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(tot[1]), "clocks": clocks,
                 "norm_after": float(nrm.item())}
         print(json.dumps(line))
     dist.destroy_process_group()
