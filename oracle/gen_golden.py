@@ -302,6 +302,23 @@ def gen_two_level():
     np.savez_compressed(os.path.join(OUT, "two_level.npz"), **out)
 
 
+def gen_qco():
+    """Compiled-code files exactly as the reference writes them (Qompiler.compile -> pickle, file_io.py:9-12)."""
+    import pickle
+    out = {}
+    for name, u, emit in (("qco_r4", None, "CTRL_PRUNED"), ("qco_cyc8", cyclic_matrix(8, 1), "SINGLET"), ("qco_r8p", None, "PRINCIPAL")):
+        seed()
+        if u is None:
+            u = random_unitary(4 if name == "qco_r4" else 8)
+        cfg = create_config(emit=emit, ancilla_offset=100, output=os.path.join(OUT, name + ".qco"))
+        qc = Qompiler(cfg, QDevice(cfg.device))
+        qc.optimizers.append(SlidingWindowCombiner(window=0, emit=cfg.emit))
+        qc.compile(u)
+        out[name + "_input"] = np.asarray(u, dtype=np.complex128)
+        print(name, os.path.getsize(os.path.join(OUT, name + ".qco")), "bytes")
+    np.savez_compressed(os.path.join(OUT, "qco_inputs.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     gen_single_gates()
@@ -310,4 +327,5 @@ if __name__ == "__main__":
     gen_streams()
     gen_qft()
     gen_two_level()
+    gen_qco()
     print("done ->", os.path.abspath(OUT))

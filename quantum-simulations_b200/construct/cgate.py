@@ -51,6 +51,19 @@ class CtrlGate:
         self._matrix = mat
         self._phase = phase
 
+    def __setstate__(self, state):
+        """Accept both this class's own pickles and the reference's (which keep the core matrix and the phase
+        inside a ``_unitary`` UnitaryM, ``cgate.py:41``)."""
+        if "_unitary" in state:
+            u = state["_unitary"]
+            self.gate = state.get("gate")
+            self.qspace = list(state["qspace"])
+            self._qontrol = dict(state["_qontrol"])
+            self._matrix = np.asarray(u.matrix)
+            self._phase = u.phase
+        else:
+            self.__dict__.update(state)
+
     # ---- structure -------------------------------------------------------------------
     def order(self) -> int:
         return 1 << len(self.qspace)

@@ -45,6 +45,13 @@ class Qubit:
     def __reduce__(self):
         return (Qubit, (self.qid, self.ancilla))
 
+    def __setstate__(self, state):
+        # a Qubit pickled by the reference (a dataclass: plain attribute dict) loading into this class
+        if isinstance(state, tuple):
+            state = state[1] or state[0]
+        self.qid = int(state["qid"])
+        self.ancilla = bool(state["ancilla"])
+
 
 def _is_qubit(x) -> bool:
     return hasattr(x, "qid") and hasattr(x, "ancilla")
