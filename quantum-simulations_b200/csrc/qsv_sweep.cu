@@ -60,7 +60,7 @@ enum : uint8_t {
 #define NONE16 0xFFFFu
 #define NONE32 0xFFFFFFFFu
 
-struct __align__(16) SwOp {  // 96 bytes = 6 x 16 B, fetched one op ahead into registers
+struct __align__(16) SwOp {  // 96 bytes = 6 x 16 B, read into registers with six 128-bit constant loads
     uint8_t type, tgt, rmask, rval;  // tgt: register bit (0..3); rmask/rval: control over the register index
     uint16_t lmask, lval;            // control over the thread's local bits (register bits excluded)
     uint64_t gmask, gval;            // control over the tile id
@@ -341,11 +341,10 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
         bool have_stage = false;
         uint64_t stq[4] = {0, 0, 0, 0};  // roffsw table of the open stage
         auto roff_of = [&](int j) { return (uint32_t)(stq[j >> 2] >> (16 * (j & 3))) & 0xFFFFu; };
-        // ops are fetched one ahead so that the constant-bank latency hides behind the previous op's math
-        OpR nxt = fetch_op(P.ops, 0);
+        // each op is read from the constant bank into registers in one go (fetching one op ahead was measured: no gain,
+        // the copy costs as much as the latency it hides)
         for (int i = 0; i < D.n_ops; ++i) {
-            const OpR op = nxt;
-            if (i + 1 < D.n_ops) nxt = fetch_op(P.ops, i + 1);
+            const OpR op = fetch_op(P.ops, i);
             const uint32_t type = op.type();
             if (type == DC_STAGE) {
                 if (have_stage) {
