@@ -46,16 +46,17 @@ enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_W =
 // and controlled/uncontrolled into ONE small integer so that the device decodes an op with a single
 // jump-table branch.
 enum : uint8_t {
+    // codes 0..14 are the lean kernel's set and are dense so that its switch compiles to one jump table
     DC_STAGE = 0,
-    DC_DENSE_REAL_NC = 1,    // +tgt (4 codes each)
+    DC_DENSE_REAL_NC = 1,    // +tgt (4 codes each); NC = no control of any kind
     DC_DENSE_CPLX_NC = 5,
-    DC_DENSE_REAL_C = 9,
-    DC_DENSE_CPLX_C = 13,
-    DC_PERMX = 17,
-    DC_HADD = 21,            // +tgt: unnormalised Hadamard butterfly (a0+a1, a0-a1); the 1/sqrt2 is folded into a later OP_TWID
-    DC_MPHASE = 25,
-    DC_W = 26,               // register-register phase table: v[j] *= W[j]
-    DC_TWID = 27,            // deferred per-register-bit phases (thread / tile dependent) + thread-wide factor + real scale
+    DC_HADD = 9,             // +tgt: unnormalised Hadamard butterfly (a0+a1, a0-a1); the 1/sqrt2 is folded into a later OP_TWID
+    DC_W = 13,               // register-register phase table: v[j] *= W[j]
+    DC_TWID = 14,            // deferred per-register-bit phases (thread / tile dependent) + thread-wide factor + real scale
+    DC_FIRST_FULL = 15,      // codes from here on exist only in the full kernel image
+    DC_DENSE_CPLX_C = 15,    // +tgt: controlled (register / thread / tile controls)
+    DC_PERMX = 19,           // +tgt
+    DC_MPHASE = 23,
 };
 #define NONE16 0xFFFFu
 #define NONE32 0xFFFFFFFFu
@@ -369,9 +370,12 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
                 }
                 continue;
             }
-            if (op.gmask && (t & op.gmask) != op.gval) continue;  // global control not satisfied for this tile
-            if (!active) continue;
-            const bool tpred = (base_l & op.lmask()) == op.lval();
+            // (threads beyond the tile's groups -- tiles smaller than a warp's worth -- run the math on garbage and never store it)
+            bool tpred = true;
+            if constexpr (!LEAN) {
+                if (op.gmask && (t & op.gmask) != op.gval) continue;  // control on a tile-id bit not satisfied for this tile
+                tpred = (base_l & op.lmask()) == op.lval();
+            }
 #define DENSE_CASES(BASE, FN, CTRL)                                   \
     case BASE + 0: FN<C, CTRL, 0>(v, op, tpred); break;               \
     case BASE + 1: FN<C, CTRL, 1>(v, op, tpred); break;               \
@@ -1136,7 +1140,7 @@ struct Builder {
         bool all_lean = true;
         for (size_t i = 0; i < e.ops.size(); ++i) {
             SwOp o = e.ops[i];
-            const bool ctrl = o.rmask || o.lmask;
+            const bool ctrl = o.rmask || o.lmask || o.gmask;
             switch (o.type) {  // builder-level kind -> device dispatch code
                 case OP_STAGE: o.type = DC_STAGE; break;
                 case OP_DENSE: {
@@ -1152,7 +1156,7 @@ struct Builder {
             }
             sp->ops[i] = o;
             const uint8_t c_ = o.type;
-            if ((c_ >= DC_DENSE_REAL_C && c_ < DC_HADD) || c_ == DC_MPHASE) all_lean = false;
+            if (c_ >= DC_FIRST_FULL) all_lean = false;
         }
         PlanStep s{};
         s.fused = true;
