@@ -41,22 +41,23 @@
 #define TSLOT_LEN 32     // one thread-phase slot = 2 chunks x 16 entries
 #define MAX_SEG 12
 
-enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_W = 4, OP_TWID = 5, OP_HADD = 6 };
+enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_W = 4, OP_TWID = 5, OP_HADD = 6, OP_HW = 7 };
 // Dispatch codes (SwOp::type as stored): the host resolves op kind, target register bit, real/complex
 // and controlled/uncontrolled into ONE small integer so that the device decodes an op with a single
 // jump-table branch.
 enum : uint8_t {
-    // codes 0..14 are the lean kernel's set and are dense so that its switch compiles to one jump table
+    // codes 0..18 are the lean kernel's set and are dense so that its switch compiles to one jump table
     DC_STAGE = 0,
     DC_DENSE_REAL_NC = 1,    // +tgt (4 codes each); NC = no control of any kind
     DC_DENSE_CPLX_NC = 5,
     DC_HADD = 9,             // +tgt: unnormalised Hadamard butterfly (a0+a1, a0-a1); the 1/sqrt2 is folded into a later OP_TWID
     DC_W = 13,               // register-register phase table: v[j] *= W[j]
     DC_TWID = 14,            // deferred per-register-bit phases (thread / tile dependent) + thread-wide factor + real scale
-    DC_FIRST_FULL = 15,      // codes from here on exist only in the full kernel image
-    DC_DENSE_CPLX_C = 15,    // +tgt: controlled (register / thread / tile controls)
-    DC_PERMX = 19,           // +tgt
-    DC_MPHASE = 23,
+    DC_HW = 15,              // +tgt: unnormalised Hadamard butterfly immediately followed by a register-register phase table
+    DC_FIRST_FULL = 19,      // codes from here on exist only in the full kernel image
+    DC_DENSE_CPLX_C = 19,    // +tgt: controlled (register / thread / tile controls)
+    DC_PERMX = 23,           // +tgt
+    DC_MPHASE = 27,
 };
 #define NONE16 0xFFFFu
 #define NONE32 0xFFFFFFFFu
@@ -406,17 +407,21 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
                 case DC_HADD + 1: op_hadd<C, 1>(v); break;
                 case DC_HADD + 2: op_hadd<C, 2>(v); break;
                 case DC_HADD + 3: op_hadd<C, 3>(v); break;
-                case DC_W: {
-                    const double2* w = smT + op.u16_at(0);
-                    const uint32_t wm = op.u16_at(2);
-#pragma unroll
-                    for (int j = 0; j < NREG; ++j)
-                        if ((wm >> j) & 1) {
-                            const double2 ww = w[j];
-                            v[j] = cmul(v[j], cmake<C, R>((R)ww.x, (R)ww.y));
-                        }
-                    break;
-                }
+#define APPLY_W()                                                              \
+    {                                                                          \
+        const double2* w = smT + op.u16_at(0);                                 \
+        const uint32_t wm = op.u16_at(2);                                      \
+        _Pragma("unroll") for (int j = 0; j < NREG; ++j) if ((wm >> j) & 1) {  \
+            const double2 ww = w[j];                                           \
+            v[j] = cmul(v[j], cmake<C, R>((R)ww.x, (R)ww.y));                  \
+        }                                                                      \
+    }
+                case DC_W: APPLY_W() break;
+                case DC_HW + 0: op_hadd<C, 0>(v); APPLY_W() break;
+                case DC_HW + 1: op_hadd<C, 1>(v); APPLY_W() break;
+                case DC_HW + 2: op_hadd<C, 2>(v); APPLY_W() break;
+                case DC_HW + 3: op_hadd<C, 3>(v); APPLY_W() break;
+#undef APPLY_W
                 case DC_TWID: {
                     const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
                     const double scale = op.m(0);
@@ -900,12 +905,19 @@ struct Builder {
                     e.tab[2 * (off + j) + 1] = std::sin(ang);
                     if (ang != 0) wm |= (uint16_t)(1u << j);
                 }
-                SwOp op;
-                memset(&op, 0, sizeof(op));
-                op.type = OP_W;
-                op.w.w_off = (uint16_t)off;
-                op.w.wmask = wm;
-                e.ops.push_back(op);
+                if (!e.ops.empty() && e.ops.back().type == OP_HADD) {
+                    // the butterfly just emitted is directly followed by this table: one op instead of two
+                    e.ops.back().type = OP_HW;
+                    e.ops.back().w.w_off = (uint16_t)off;
+                    e.ops.back().w.wmask = wm;
+                } else {
+                    SwOp op;
+                    memset(&op, 0, sizeof(op));
+                    op.type = OP_W;
+                    op.w.w_off = (uint16_t)off;
+                    op.w.wmask = wm;
+                    e.ops.push_back(op);
+                }
             }
         }
         if (!fallbacks.empty()) {
@@ -1151,6 +1163,7 @@ struct Builder {
                 case OP_PERMX: o.type = (uint8_t)(DC_PERMX + o.tgt); break;
                 case OP_MPHASE: o.type = DC_MPHASE; break;
                 case OP_HADD: o.type = (uint8_t)(DC_HADD + o.tgt); break;
+                case OP_HW: o.type = (uint8_t)(DC_HW + o.tgt); break;
                 case OP_W: o.type = DC_W; break;
                 default: o.type = DC_TWID; break;
             }
