@@ -164,6 +164,13 @@ int qsv_permute_bits(qsv_ctx* ctx, const void* in, void* out, int n_bits, const 
 int qsv_compare(qsv_ctx* ctx, const void* a, const void* b, uint64_t n_amps, double rtol,
                 double atol, double* out_max, uint64_t* out_bad, void* stream);
 
+/* Equality up to one complex scalar: *out_ok = 1 iff a == lambda * b within |a - lambda b| <= atol + rtol |lambda b|,
+ * lambda = a[i]/b[i] at the first i with |b[i]| > 1e-8 (lambda = 0 if there is none), returned in out_ratio[2] (re, im).
+ * Synchronises `stream`.  Replaces allprop (quompiler/utils/mfun.py:34-52), the check the reference's PRINCIPAL-level
+ * builder tests use (tests/qompiler/circuits/test_cirq_circuit.py:52).                                           */
+int qsv_allprop(qsv_ctx* ctx, const void* a, const void* b, uint64_t n_amps, double rtol, double atol,
+                int* out_ok, double* out_ratio, void* stream);
+
 /* Same result as qsv_compare, for callers that must not allocate.  No counterpart in the
  * reference.  It needs no context and calls no cudaMalloc/cudaFree (nor any routine that does):
  * its scratch is a fixed array inside the library, about 16 KiB on every GPU that loads

@@ -51,6 +51,8 @@ _SIGNATURES = {
     "qsv_permute_bits": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "qsv_compare": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_double,
                               C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_void_p]),
+    "qsv_allprop": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_double, C.POINTER(C.c_int),
+                              C.POINTER(C.c_double), C.c_void_p]),
     "qsv_compare_noalloc": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_double, C.c_double,
                                       C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_void_p]),
 }

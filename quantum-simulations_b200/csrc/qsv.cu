@@ -294,6 +294,56 @@ __global__ void __launch_bounds__(256) k_compare_final(const double* __restrict_
     }
 }
 
+// first index whose entry is not ~0 (|b| > atol), and compare against a scaled second operand: the two pieces of
+// the reference's allprop (quompiler/utils/mfun.py:34-52)
+template <typename R>
+__global__ void __launch_bounds__(256) k_first_nonzero(const typename cplx_of<R>::type* __restrict__ b, uint64_t n, double atol,
+                                                       unsigned long long* __restrict__ out) {
+    typedef typename cplx_of<R>::type C;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    unsigned long long best = ~0ull;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const C y = b[i];
+        if (!(hypot((double)y.x, (double)y.y) <= atol)) {
+            best = i;
+            break;  // indexes only grow along this thread's stride
+        }
+    }
+    if (best != ~0ull) atomicMin(out, best);
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256) k_compare_scaled(const typename cplx_of<R>::type* __restrict__ a,
+                                                        const typename cplx_of<R>::type* __restrict__ b, uint64_t n, double lre,
+                                                        double lim, double rtol, double atol, double* __restrict__ partial) {
+    typedef typename cplx_of<R>::type C;
+    double mx = 0.0, bad = 0.0;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const C x = a[i], y = b[i];
+        const double sx = lre * (double)y.x - lim * (double)y.y, sy = lre * (double)y.y + lim * (double)y.x;
+        const double d = hypot((double)x.x - sx, (double)x.y - sy);
+        if (!(d <= atol + rtol * hypot(sx, sy))) bad += 1.0;
+        if (!(d <= mx)) mx = d;
+    }
+    __shared__ double smx[256], sbad[256];
+    smx[threadIdx.x] = mx;
+    sbad[threadIdx.x] = bad;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) {
+            const double o = smx[threadIdx.x + s];
+            if (!(o <= smx[threadIdx.x])) smx[threadIdx.x] = o;
+            sbad[threadIdx.x] += sbad[threadIdx.x + s];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        partial[2 * blockIdx.x] = smx[0];
+        partial[2 * blockIdx.x + 1] = sbad[0];
+    }
+}
+
 // ================================================================================================
 // host side
 // ================================================================================================
@@ -777,6 +827,65 @@ int qsv_compare(qsv_ctx* ctx, const void* a, const void* b, uint64_t n_amps, dou
     return QSV_OK;
 }
 
+
+int qsv_allprop(qsv_ctx* ctx, const void* a, const void* b, uint64_t n_amps, double rtol, double atol, int* out_ok,
+                double* out_ratio, void* stream) {
+    if (!ctx) return QSV_E_INVALID;
+    if (n_amps && (!a || !b)) return qsv_fail(ctx, QSV_E_INVALID, "NULL buffer");
+    cudaStream_t s = (cudaStream_t)stream;
+    QSV_CUDA(ctx, cudaSetDevice(ctx->device));
+    const bool dbl = ctx->dtype == QSV_C128;
+    const size_t amp = amp_size(ctx->dtype);
+    double ratio[2] = {0.0, 0.0};
+    double res[2] = {0.0, 0.0};
+    if (n_amps) {
+        const int blocks = (int)std::min<uint64_t>((n_amps + 255) / 256, CMP_BLOCKS);
+        double* partial = ctx->d_red;
+        double* result = ctx->d_red + 2 * CMP_BLOCKS;
+        unsigned long long* d_idx = reinterpret_cast<unsigned long long*>(result);
+        unsigned long long idx = ~0ull;
+        QSV_CUDA(ctx, cudaMemsetAsync(d_idx, 0xFF, sizeof(unsigned long long), s));
+        if (dbl) k_first_nonzero<double><<<blocks, 256, 0, s>>>((const double2*)b, n_amps, 1e-8, d_idx);
+        else k_first_nonzero<float><<<blocks, 256, 0, s>>>((const float2*)b, n_amps, 1e-8, d_idx);
+        QSV_CUDA(ctx, cudaGetLastError());
+        QSV_CUDA(ctx, cudaMemcpyAsync(&idx, d_idx, sizeof(idx), cudaMemcpyDeviceToHost, s));
+        QSV_CUDA(ctx, cudaStreamSynchronize(s));
+        ctx->stats.kernel_launches++;
+        if (idx != ~0ull) {  // ratio = a[idx] / b[idx], as mfun.py:50
+            double av[2], bv[2];
+            if (dbl) {
+                QSV_CUDA(ctx, cudaMemcpyAsync(av, (const char*)a + idx * amp, 16, cudaMemcpyDeviceToHost, s));
+                QSV_CUDA(ctx, cudaMemcpyAsync(bv, (const char*)b + idx * amp, 16, cudaMemcpyDeviceToHost, s));
+                QSV_CUDA(ctx, cudaStreamSynchronize(s));
+            } else {
+                float af[2], bf[2];
+                QSV_CUDA(ctx, cudaMemcpyAsync(af, (const char*)a + idx * amp, 8, cudaMemcpyDeviceToHost, s));
+                QSV_CUDA(ctx, cudaMemcpyAsync(bf, (const char*)b + idx * amp, 8, cudaMemcpyDeviceToHost, s));
+                QSV_CUDA(ctx, cudaStreamSynchronize(s));
+                av[0] = af[0]; av[1] = af[1]; bv[0] = bf[0]; bv[1] = bf[1];
+            }
+            const double den = bv[0] * bv[0] + bv[1] * bv[1];
+            ratio[0] = (av[0] * bv[0] + av[1] * bv[1]) / den;
+            ratio[1] = (av[1] * bv[0] - av[0] * bv[1]) / den;
+        }
+        // b ~ 0 everywhere: proportional iff a ~ 0 too (ratio 0), which the scaled compare with lambda = 0 checks
+        if (dbl)
+            k_compare_scaled<double><<<blocks, 256, 0, s>>>((const double2*)a, (const double2*)b, n_amps, ratio[0], ratio[1], rtol, atol, partial);
+        else
+            k_compare_scaled<float><<<blocks, 256, 0, s>>>((const float2*)a, (const float2*)b, n_amps, ratio[0], ratio[1], rtol, atol, partial);
+        k_compare_final<<<1, 256, 0, s>>>(partial, blocks, result);
+        ctx->stats.kernel_launches += 2;
+        QSV_CUDA(ctx, cudaGetLastError());
+        QSV_CUDA(ctx, cudaMemcpyAsync(res, result, sizeof(res), cudaMemcpyDeviceToHost, s));
+        QSV_CUDA(ctx, cudaStreamSynchronize(s));
+    }
+    if (out_ok) *out_ok = res[1] == 0.0;
+    if (out_ratio) {
+        out_ratio[0] = ratio[0];
+        out_ratio[1] = ratio[1];
+    }
+    return QSV_OK;
+}
 
 // ------------------------------------------------------------------------------------------------
 // Allocation-free compare.

@@ -160,6 +160,15 @@ class Engine:
                                    C.byref(mx), C.byref(bad), self._stream()), self._ctx)
         return mx.value, int(bad.value)
 
+    def allprop(self, a, b, rtol=1e-5, atol=1e-8):
+        """(ok, ratio): is ``a == ratio * b`` for one complex scalar?  Device version of the reference's allprop."""
+        assert a.numel() == b.numel()
+        ok = C.c_int(0)
+        ratio = (C.c_double * 2)()
+        check(self.lib.qsv_allprop(self._ctx, C.c_void_p(a.data_ptr()), C.c_void_p(b.data_ptr()), a.numel(), rtol, atol,
+                                   C.byref(ok), ratio, self._stream()), self._ctx)
+        return bool(ok.value), complex(ratio[0], ratio[1])
+
     def allclose(self, a, b, rtol=1e-5, atol=1e-8) -> bool:
         return self.compare(a, b, rtol, atol)[1] == 0
 

@@ -396,3 +396,29 @@ def test_rowslab_permutation_streams_bit_exact():
         assert eng.fuse() == 1
         res = eng.run(st, None).view(1 << n, 1 << n).cpu().numpy()
         assert np.array_equal(res, d[f"{name}_value"])
+
+
+def test_allprop_on_device():
+    """Equality up to a phase (the reference's allprop, mfun.py:34-52), as used by the PRINCIPAL-level builder checks."""
+    import torch
+    eng = get_engine()
+    d = load("streams")
+    leaves = unpack_gates(d, "r4principal")
+    got = reconstruct_unitary(leaves[::-1], drop_ancilla=True)
+    lam = np.exp(0.7j)
+    a = torch.from_numpy(np.ascontiguousarray(lam * got).reshape(-1)).cuda()
+    b = torch.from_numpy(np.ascontiguousarray(d["r4principal_input"]).reshape(-1)).cuda()
+    ok, ratio = eng.allprop(a, b)
+    assert ok and abs(ratio - lam) < 1e-9
+    a2 = a.clone()
+    a2[5] += 1e-3
+    assert not eng.allprop(a2, b)[0]
+    z = torch.zeros_like(b)
+    assert eng.allprop(z, z) == (True, 0j)          # b ~ 0: proportional iff a ~ 0, ratio 0
+    assert not eng.allprop(a, z)[0]
+    # leading zeros in b: the ratio is taken at the first entry that is not ~0
+    b3 = b.clone()
+    b3[:3] = 0
+    a3 = (2.5 - 1j) * b3
+    ok, ratio = eng.allprop(a3, b3)
+    assert ok and abs(ratio - (2.5 - 1j)) < 1e-12
