@@ -413,10 +413,15 @@ class ShardedCircuit:
                 self._keys.append(li)
                 li += 1
 
-    def apply(self, state, spare):
-        """Returns (state, spare) -- the buffers may have traded places."""
+    def apply(self, state, spare, timers=None):
+        """Returns (state, spare) -- the buffers may have traded places.  ``timers`` (a list) collects one
+        ``(step kind, start event, end event)`` per plan step, recorded on the current CUDA stream."""
         li = 0
         for s in self.plan.steps:
+            if timers is not None:
+                import torch
+                e0 = torch.cuda.Event(enable_timing=True)
+                e0.record()
             if s[0] == "local":
                 state, spare = self.executor.run_segment(self._keys[li], state, spare)
                 li += 1
@@ -426,6 +431,10 @@ class ShardedCircuit:
                 state, spare = self.exchanger.exchange_all(state, spare)
             else:
                 state, spare = self.executor.permute(state, spare, self.n_loc, s[1])
+            if timers is not None:
+                e1 = torch.cuda.Event(enable_timing=True)
+                e1.record()
+                timers.append((s[0], e0, e1))
         return state, spare
 
 
@@ -488,6 +497,17 @@ def bench_main(args):
     st = execu.total_stats()
     tot = torch.tensor([st.get("amp_bytes", 0), st.get("kernel_launches", 0), exch.bytes_sent], device=dev, dtype=torch.float64)
     dist.all_reduce(tot)
+    # one more, untimed, step with CUDA events around every plan step: where the time goes, and the NVLink rate
+    timers = []
+    dist.barrier()
+    state, spare = circ.apply(state, spare, timers)
+    torch.cuda.synchronize()
+    split = {}
+    for kind, a, b in timers:
+        split[kind] = split.get(kind, 0.0) + a.elapsed_time(b)
+    sp_t = torch.tensor([split.get("local", 0.0), split.get("permute", 0.0), split.get("xall", 0.0) + split.get("exchange", 0.0)],
+                        device=dev, dtype=torch.float64)
+    dist.all_reduce(sp_t, op=dist.ReduceOp.MAX)
     # norm check (unitarity) as a cheap correctness guard of the whole sharded run
     nrm = torch.linalg.vector_norm(state) ** 2
     dist.all_reduce(nrm)
@@ -532,7 +552,12 @@ def bench_main(args):
                 "roofline": {"bound": "hbm", "kernel": "k_sweep (fused tile sweep), aggregate over ranks incl. exchange time",
                              "achieved": amp_gbps / world, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                              "frac": amp_gbps / world / peak, "traffic": None},
-                "nvlink": {"bytes_sent_per_rank_per_step": float(tot[2]) / world / args.steps, "exchanges_per_step": n_ex},
+                "nvlink": {"bytes_sent_per_rank_per_step": float(tot[2]) / world / args.steps, "exchanges_per_step": n_ex,
+                           "exchange_ms_per_step": float(sp_t[2]),
+                           "achieved_GBps_per_direction_per_gpu": (float(tot[2]) / world / args.steps) / (float(sp_t[2]) * 1e-3) / 1e9 if float(sp_t[2]) > 0 else None,
+                           "peak_GBps": 770.0, "peak_source": "measured peer copy per direction (B200_PROFILING.md); nominal 900",
+                           "frac": ((float(tot[2]) / world / args.steps) / (float(sp_t[2]) * 1e-3) / 1e9 / 770.0) if float(sp_t[2]) > 0 else None},
+                "ms_split_one_step": {"local_sweeps": float(sp_t[0]), "local_permutes": float(sp_t[1]), "exchanges": float(sp_t[2])},
                 "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(tot[1]), "clocks": clocks,
                 "norm_after": float(nrm.item())}
         print(json.dumps(line))
