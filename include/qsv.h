@@ -158,6 +158,16 @@ int qsv_project_ancilla(qsv_ctx* ctx, const void* in, void* out, int n_bits, int
  * quompiler/utils/permute.py:60-121); also the local half of a qubit remap.         */
 int qsv_permute_bits(qsv_ctx* ctx, const void* in, void* out, int n_bits, const int* perm,
                      void* stream);
+/* Multi-GPU exchange fused with the local bit permutation (one kernel, no NCCL): the shard `in` of 2^n_bits
+ * amplitudes on rank `rank` is bit-permuted (perm as in qsv_permute_bits) and every result is stored straight into
+ * the destination rank's buffer over NVLink: the top g_bits bits of the permuted index select the rank
+ * (peer_out[0 .. 2^g_bits), peer-mapped device pointers to every rank's destination buffer, peer_out[rank] being this
+ * rank's own), and `rank` takes their place in the address there -- i.e. the all-to-all "global bits <-> top local
+ * bits" of the sharded state vector.  The caller synchronises the ranks before the destination buffers are read
+ * (and before they are written again).  No reference counterpart (the reference is single process).            */
+int qsv_permute_exchange(qsv_ctx* ctx, const void* in, void* const* peer_out, int g_bits, int rank, int n_bits,
+                         const int* perm, void* stream);
+
 /* *out_max = max_i |a[i] - b[i]| (complex modulus) and *out_bad = number of entries
  * with |a-b| > atol + rtol*|b|.  Synchronises `stream`.  Replaces np.allclose(v, u)
  * (tests/qompiler/circuits/test_qompiler.py:82, quompiler/utils/mfun.py:34-52).      */

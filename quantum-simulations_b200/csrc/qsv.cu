@@ -801,6 +801,35 @@ int qsv_permute_bits(qsv_ctx* ctx, const void* in, void* out, int n_bits, const 
     return QSV_OK;
 }
 
+int qsv_permute_exchange(qsv_ctx* ctx, const void* in, void* const* peer_out, int g_bits, int rank, int n_bits, const int* perm,
+                         void* stream) {
+    if (!ctx) return QSV_E_INVALID;
+    if (!in || !peer_out || !perm) return qsv_fail(ctx, QSV_E_INVALID, "NULL argument");
+    if (g_bits < 1 || g_bits > 3) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "g_bits=%d: 2, 4 or 8 ranks are supported", g_bits);
+    if (rank < 0 || rank >= (1 << g_bits)) return qsv_fail(ctx, QSV_E_INVALID, "rank %d out of range", rank);
+    if (n_bits < 9 || n_bits > 62 || n_bits < 2 * g_bits) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "local shard of 2^%d amplitudes is too small for the fused exchange", n_bits);
+    uint64_t seen = 0;
+    uint64_t peers[8] = {0};
+    for (int i = 0; i < n_bits; ++i) {
+        if (perm[i] < 0 || perm[i] >= n_bits || (seen & (1ull << perm[i]))) return qsv_fail(ctx, QSV_E_INVALID, "perm is not a permutation");
+        seen |= 1ull << perm[i];
+    }
+    for (int i = 0; i < (1 << g_bits); ++i) {
+        if (!peer_out[i]) return qsv_fail(ctx, QSV_E_INVALID, "peer buffer %d is NULL", i);
+        if (peer_out[i] == in) return qsv_fail(ctx, QSV_E_INVALID, "the exchange is out of place: peer buffer %d aliases the input", i);
+        peers[i] = (uint64_t)peer_out[i];
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    QSV_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = sweep_permute_run(ctx, in, peer_out[rank], n_bits, perm, s, g_bits, rank, peers);
+    if (rc == QSV_E_UNSUPPORTED) return qsv_fail(ctx, rc, "unsupported: permutation needs more tile bits than available");
+    if (rc) return rc;
+    ctx->stats.kernel_launches++;
+    ctx->stats.sweeps++;
+    ctx->stats.amp_bytes += 2 * (amp_size(ctx->dtype) << n_bits);
+    return QSV_OK;
+}
+
 int qsv_compare(qsv_ctx* ctx, const void* a, const void* b, uint64_t n_amps, double rtol, double atol, double* out_max,
                 uint64_t* out_bad, void* stream) {
     if (!ctx) return QSV_E_INVALID;

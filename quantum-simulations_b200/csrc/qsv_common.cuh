@@ -100,4 +100,5 @@ int sweep_plan_collect_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out);
 void rowslab_free(RowSlabPlan* p);
 int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out);
 int rowslab_run(qsv_ctx* ctx, RowSlabPlan* plan, void* state, cudaStream_t stream);
-int sweep_permute_run(qsv_ctx* ctx, const void* in, void* out, int n_bits, const int* perm, cudaStream_t stream);
+int sweep_permute_run(qsv_ctx* ctx, const void* in, void* out, int n_bits, const int* perm, cudaStream_t stream, int xg = 0,
+                      int xrank = 0, const uint64_t* peers = nullptr);

@@ -113,6 +113,12 @@ struct SweepDesc {
     uint8_t direct_load, direct_store;
     uint8_t first_rpos[RB], last_rpos[RB];
     uint32_t tab_off, tab_len;              // shared phase tables: aux offset / length in double2 units
+    // Fused exchange (multi-GPU): when xg > 0 the store does not go to `dst` but straight into the peers' buffers over
+    // NVLink -- the top xg bits of the (permuted) output index select the destination rank, and this rank's id takes
+    // their place in the address there.  That is the all-to-all "global bits <-> top local bits" done by the sweep's
+    // own stores: no NCCL call and no extra pass over the shard.
+    int xg, xrank;
+    uint64_t peer[8];                       // device address of every rank's destination buffer (peer-mapped)
 };
 
 struct SweepParams {
@@ -484,7 +490,16 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
                 if (i < n_slots) v[i] = tile[t_st_s ^ D.st_soff[i]];
 #pragma unroll
             for (int i = 0; i < NREG; ++i)
-                if (i < n_slots) dst[gb | D.st_goff[i]] = v[i];
+                if (i < n_slots) {
+                    const uint64_t y = gb | D.st_goff[i];
+                    if (D.xg) {
+                        const int sh = D.n_bits - D.xg;
+                        C* pd = reinterpret_cast<C*>(D.peer[y >> sh]);
+                        pd[((uint64_t)D.xrank << sh) | (y & ((1ull << sh) - 1ull))] = v[i];
+                    } else {
+                        dst[y] = v[i];
+                    }
+                }
         }
         __syncthreads();  // this buffer and the per-tile scalars are rewritten two / one tiles from now
         cur ^= 1;
@@ -1429,7 +1444,8 @@ static int sweep_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, 
 
 // Bit permutation as ONE gate-free tile sweep with a permuting store: out[y] = in[x], bit perm[i] of y = bit i of x.
 // Returns QSV_E_UNSUPPORTED when the state is too small for the tile machinery (caller falls back to k_permute_bits).
-int sweep_permute_run(qsv_ctx* ctx, const void* in, void* out, int n_bits, const int* perm, cudaStream_t stream) {
+int sweep_permute_run(qsv_ctx* ctx, const void* in, void* out, int n_bits, const int* perm, cudaStream_t stream, int xg, int xrank,
+                      const uint64_t* peers) {
     if (n_bits < 9) return QSV_E_UNSUPPORTED;
     const int k = std::min(n_bits, 11);
     SweepPlan tmp;
@@ -1460,6 +1476,12 @@ int sweep_permute_run(qsv_ctx* ctx, const void* in, void* out, int n_bits, const
     if (rc) return rc;
     rc = sweep_set_smem_attr(ctx, k);
     if (rc) return rc;
+    if (xg > 0) {
+        SweepDesc& D = tmp.steps[0].params->d;
+        D.xg = xg;
+        D.xrank = xrank;
+        for (int i = 0; i < (1 << xg); ++i) D.peer[i] = peers[i];
+    }
     rc = sweep_launch(ctx, n_bits, k, in, out, nullptr, *tmp.steps[0].params, stream);
     if (rc) return rc;
     ctx->stats.fused_sweeps++;

@@ -7,9 +7,11 @@ on one of those *global* bits; then
  * a control on a global bit costs nothing: the rank either takes part or skips the gate;
  * a diagonal gate with a global target costs nothing: the rank's bit picks ``d0`` or ``d1`` and the
    gate becomes a scalar phase on the (locally) controlled subspace;
- * any other gate needs ONE exchange step: the global bit is swapped with the top local bit by a
-   pairwise half-state swap with partner ``rank ^ (1 << bit)`` (NCCL send/recv over NVLink through
-   ``torch.distributed``), after which the qubit is local; a bit-position table tracks the remap.
+ * any other gate needs ONE exchange step: all g global bits trade places with the top g local bits
+   (an NCCL all-to-all over NVLink through ``torch.distributed``; with one global bit this is the
+   pairwise half-state swap with partner ``rank ^ 1``, which ``TorchExchanger.exchange`` also offers for
+   a single bit), after which the qubits are local; a bit-position table tracks the remap and the
+   evicted bits are chosen by furthest next use.
 
 The planner below is host logic and identical on every rank (the exchange sequence must be); it cuts
 the gate stream into local segments separated by exchanges and restores the canonical layout at the
@@ -31,7 +33,7 @@ from ._lib import DIAG1, GATE_DTYPE, PERMX, ROWS2
 # planning (rank independent)
 # ---------------------------------------------------------------------------------------------
 class ShardPlan:
-    """steps: ("local", [record indexes]) | ("exchange", global_bit) | ("permute", perm_list)."""
+    """steps: ("local", [record indexes]) | ("xall",) | ("exchange", global_bit) | ("permute", perm_list)."""
 
     def __init__(self, n_bits, g_bits):
         self.n_bits = n_bits
@@ -119,8 +121,7 @@ def plan_sharded(recs, n_bits, g_bits, restore=True, relabel_swaps=True) -> Shar
         else:
             i += 1
     uses = [[] for _ in range(n_bits)]     # per logical bit: record indexes where it is a non-diagonal target
-    label = list(range(n_bits))            # relabel-aware: which CURRENT logical name a future use refers to
-    # (uses are recorded against the logical bit named in the record; relabels rename data, handled below)
+    # (uses are recorded against the logical bit named in the record; relabels rename data, see next_use)
     skip = set()
     for i0, (a, b) in swap_at.items():
         skip.update((i0, i0 + 1, i0 + 2))
@@ -136,7 +137,6 @@ def plan_sharded(recs, n_bits, g_bits, restore=True, relabel_swaps=True) -> Shar
         """Index of the next record (>= i) that needs logical bit b as a non-diagonal target.  SWAP relabels
         between now and then rename the data, so follow them: the data now called b is called tau(b) later."""
         name = b
-        best = None
         # walk forward through relabels in order; between relabels look up uses of the current name
         pos_i = i
         for s_i in sorted(k_ for k_ in swap_at if k_ >= i):
