@@ -340,6 +340,7 @@ def main():
     ap.add_argument("--no-fuse", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=6)
     ap.add_argument("--cpu-gates", type=int, default=12, help="gates in the CPU baseline sample (0 = skip)")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "fused", "nccl"], help="multi-GPU exchange engine")
     ap.add_argument("--circuit", default="qft", help="qft | hlayer:LO:HI (diagnostic)")
     args = ap.parse_args()
     global CIRCUIT

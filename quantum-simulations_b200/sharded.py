@@ -339,6 +339,55 @@ def _exchange_all(dist, state, spare, world):
     return spare, state
 
 
+class SymmExchanger:
+    """Exchange step as ONE CUDA kernel over peer memory (no NCCL): the gate-free permuting sweep that parks the
+    victims is given every rank's destination buffer (torch symmetric memory = peer-mapped allocations) and stores
+    each amplitude straight into the rank that will own it (``qsv_permute_exchange``).  Two signal-pad barriers
+    bracket the kernel: all ranks have stopped using the destination buffers / all stores have landed."""
+
+    def __init__(self, rank, world, n_amps, device):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        self.rank, self.world = rank, world
+        self.g = world.bit_length() - 1
+        self.bytes_sent = 0
+        group = dist.group.WORLD
+        try:
+            symm_mem.enable_symm_mem_for_group(group.group_name)
+        except Exception:
+            pass
+        self.bufs = []
+        self.peers = {}
+        self.handles = {}
+        for _ in range(2):
+            raw = symm_mem.empty(2 * n_amps, dtype=torch.float64, device=device)
+            hdl = symm_mem.rendezvous(raw, group)
+            t = torch.view_as_complex(raw.view(-1, 2))
+            self.bufs.append(t)
+            self.peers[t.data_ptr()] = [int(p) for p in hdl.buffer_ptrs]
+            self.handles[t.data_ptr()] = hdl
+        self._raw = None
+
+    def buffers(self):
+        return self.bufs[0], self.bufs[1]
+
+    def permute_exchange(self, executor, state, spare, n_loc, perm):
+        import ctypes as C
+        from ._lib import check
+        eng = executor.any_engine()
+        peers = self.peers[spare.data_ptr()]
+        arr = (C.c_void_p * self.world)(*peers)
+        p = np.ascontiguousarray(perm, dtype=np.int32)
+        hdl = self.handles[spare.data_ptr()]
+        hdl.barrier(channel=0)      # every rank has finished whatever still touched its destination buffer
+        check(eng.lib.qsv_permute_exchange(eng._ctx, C.c_void_p(state.data_ptr()), arr, self.g, self.rank, n_loc,
+                                           p.ctypes.data_as(C.c_void_p), eng._stream()), eng._ctx)
+        hdl.barrier(channel=1)      # every rank's stores have landed
+        self.bytes_sent += state.numel() * state.element_size() * (self.world - 1) // self.world
+        return spare, state
+
+
 class GpuExecutor:
     """Runs local segments on the CUDA engine; one libqsv context (with its fused plan) per segment."""
 
@@ -381,6 +430,12 @@ class GpuExecutor:
                                        p.ctypes.data_as(C.c_void_p), eng._stream()), eng._ctx)
         return spare, state
 
+    def any_engine(self):
+        if not self.engines:
+            from .engine import Engine
+            self.engines["_perm"] = (Engine(self.device, np.complex128), False)
+        return next(iter(self.engines.values()))[0]
+
     def total_stats(self):
         tot = {}
         for eng, _ in self.engines.values():
@@ -417,12 +472,27 @@ class ShardedCircuit:
         """Returns (state, spare) -- the buffers may have traded places.  ``timers`` (a list) collects one
         ``(step kind, start event, end event)`` per plan step, recorded on the current CUDA stream."""
         li = 0
-        for s in self.plan.steps:
+        fused_x = hasattr(self.exchanger, "permute_exchange")
+        steps = self.plan.steps
+        k = 0
+        while k < len(steps):
+            s = steps[k]
+            k += 1
+            if fused_x and s[0] in ("permute", "xall"):
+                # (local permutation, exchange) or a bare exchange -> one kernel storing into the peers' buffers
+                if s[0] == "permute" and k < len(steps) and steps[k][0] == "xall":
+                    perm = s[1]
+                    k += 1
+                    s = ("pxall", perm)
+                elif s[0] == "xall":
+                    s = ("pxall", list(range(self.n_loc)))
             if timers is not None:
                 import torch
                 e0 = torch.cuda.Event(enable_timing=True)
                 e0.record()
-            if s[0] == "local":
+            if s[0] == "pxall":
+                state, spare = self.exchanger.permute_exchange(self.executor, state, spare, self.n_loc, s[1])
+            elif s[0] == "local":
                 state, spare = self.executor.run_segment(self._keys[li], state, spare)
                 li += 1
             elif s[0] == "exchange":
@@ -434,7 +504,7 @@ class ShardedCircuit:
             if timers is not None:
                 e1 = torch.cuda.Event(enable_timing=True)
                 e1.record()
-                timers.append((s[0], e0, e1))
+                timers.append(("xall" if s[0] == "pxall" else s[0], e0, e1))
         return state, spare
 
 
@@ -459,8 +529,29 @@ def bench_main(args):
     n_loc = n - g
     amps = 1 << n_loc
     dev = f"cuda:{local_rank}"
-    state = torch.empty(amps, dtype=torch.complex128, device=dev)
-    spare = torch.empty(amps, dtype=torch.complex128, device=dev)
+    # exchange engine: the fused peer-memory kernel when torch symmetric memory works here, else NCCL all-to-all
+    exch = None
+    exch_kind = "nccl all_to_all"
+    if getattr(args, "exchange", "auto") in ("auto", "fused"):
+        try:
+            exch = SymmExchanger(rank, world, amps, torch.device(dev))
+            exch_kind = "fused permute+exchange kernel over peer memory (torch symmetric memory)"
+        except Exception as e:  # noqa: BLE001
+            if args.exchange == "fused":
+                raise
+            if rank == 0:
+                print(f"[bench] symmetric memory unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+            exch = None
+    ok = torch.tensor([1 if exch is not None else 0], device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if int(ok.item()) == 0:
+        exch = None
+        exch_kind = "nccl all_to_all"
+    if exch is not None:
+        state, spare = exch.buffers()
+    else:
+        state = torch.empty(amps, dtype=torch.complex128, device=dev)
+        spare = torch.empty(amps, dtype=torch.complex128, device=dev)
     gen = torch.Generator(device=dev)
     gen.manual_seed(42 + rank)
     view = torch.view_as_real(state)
@@ -471,7 +562,8 @@ def bench_main(args):
     dist.all_reduce(nrm)
     state.div_(torch.sqrt(nrm))
     execu = GpuExecutor(local_rank, fuse=not args.no_fuse, tile_bits=args.tile_bits)
-    exch = TorchExchanger(rank, world)
+    if exch is None:
+        exch = TorchExchanger(rank, world)
     circ = ShardedCircuit(recs, pool, n, rank, world, execu, exch)
     for _ in range(args.warmup):
         state, spare = circ.apply(state, spare)
@@ -546,7 +638,7 @@ def bench_main(args):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "c128", "data": "synthetic",
                 "config": {"workload": f"qft{n}_statevector_c128", "qubits": n, "amplitudes": 1 << n, "gates": circ.n_gates,
-                           "sharding": f"top {g} qubits over {world} GPUs", "exchanges_per_step": n_ex,
+                           "sharding": f"top {g} qubits over {world} GPUs", "exchanges_per_step": n_ex, "exchange": exch_kind,
                            "local_amplitudes": amps, "l2": "local shard far larger than the 126 MB L2" if amps * 16 > (1 << 28) else "local shard fits L2"},
                 "amp_GBps": amp_gbps, "hbm_frac_of_measured": amp_gbps / (peak * world),
                 "roofline": {"bound": "hbm", "kernel": "k_sweep (fused tile sweep), aggregate over ranks incl. exchange time",
