@@ -353,10 +353,6 @@ class SymmExchanger:
         self.g = world.bit_length() - 1
         self.bytes_sent = 0
         group = dist.group.WORLD
-        try:
-            symm_mem.enable_symm_mem_for_group(group.group_name)
-        except Exception:
-            pass
         self.bufs = []
         self.peers = {}
         self.handles = {}
