@@ -528,7 +528,10 @@ def bench_main(args):
     # exchange engine: the fused peer-memory kernel when torch symmetric memory works here, else NCCL all-to-all
     exch = None
     exch_kind = "nccl all_to_all"
-    if getattr(args, "exchange", "auto") in ("auto", "fused"):
+    # measured (profiles/README.md): direct peer stores beat NCCL on 2 GPUs (45.8 vs 60.7 ms QFT-30), tie on 4 and
+    # lose on 8 (390 vs 656 GB/s per direction per GPU), so "auto" takes the direct engine up to 4 ranks only
+    want = getattr(args, "exchange", "auto")
+    if want == "fused" or (want == "auto" and world <= 4):
         try:
             exch = SymmExchanger(rank, world, amps, torch.device(dev))
             exch_kind = "fused permute+exchange kernel over peer memory (torch symmetric memory)"
