@@ -17,11 +17,11 @@ template <> struct cplx_of<double> { typedef double2 type; };
 template <> struct cplx_of<float>  { typedef float2 type; };
 
 template <typename C, typename R>
-__device__ __forceinline__ C cmake(R x, R y) { C c; c.x = x; c.y = y; return c; }
+__host__ __device__ __forceinline__ C cmake(R x, R y) { C c; c.x = x; c.y = y; return c; }
 
 // a*b, written so that multiplication by an exact (1,0) returns a unchanged
 template <typename C>
-__device__ __forceinline__ C cmul(const C a, const C b) {
+__host__ __device__ __forceinline__ C cmul(const C a, const C b) {
     C r;
     r.x = a.x * b.x - a.y * b.y;
     r.y = a.x * b.y + a.y * b.x;
@@ -29,7 +29,7 @@ __device__ __forceinline__ C cmul(const C a, const C b) {
 }
 // acc + a*b
 template <typename C>
-__device__ __forceinline__ C cfma(const C a, const C b, const C acc) {
+__host__ __device__ __forceinline__ C cfma(const C a, const C b, const C acc) {
     C r;
     r.x = fma(a.x, b.x, fma(-a.y, b.y, acc.x));
     r.y = fma(a.x, b.y, fma(a.y, b.x, acc.y));

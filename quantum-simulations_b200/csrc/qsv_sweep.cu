@@ -41,7 +41,7 @@
 #define TSLOT_LEN 32     // one thread-phase slot = 2 chunks x 16 entries
 #define MAX_SEG 12
 
-enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_W = 4, OP_TWID = 5, OP_HADD = 6, OP_HW = 7 };
+enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_W = 4, OP_TWID = 5, OP_HADD = 6, OP_HW = 7, OP_FSTAGE = 8 };
 // Dispatch codes (SwOp::type as stored): the host resolves op kind, target register bit, real/complex
 // and controlled/uncontrolled into ONE small integer so that the device decodes an op with a single
 // jump-table branch.
@@ -54,10 +54,12 @@ enum : uint8_t {
     DC_W = 13,               // register-register phase table: v[j] *= W[j]
     DC_TWID = 14,            // deferred per-register-bit phases (thread / tile dependent) + thread-wide factor + real scale
     DC_HW = 15,              // +tgt: unnormalised Hadamard butterfly immediately followed by a register-register phase table
-    DC_FIRST_FULL = 19,      // codes from here on exist only in the full kernel image
-    DC_DENSE_CPLX_C = 19,    // +tgt: controlled (register / thread / tile controls)
-    DC_PERMX = 23,           // +tgt
-    DC_MPHASE = 27,
+    DC_FSTAGE = 19,          // +shape (10 codes): a whole register stage of the "FFT shape" as ONE straight-line op (see
+                             // fstage_math); runs only in the IMG_FFT kernel image, whose launches hold nothing else
+    DC_FIRST_FULL = 29,      // codes from here on exist only in the full kernel image
+    DC_DENSE_CPLX_C = 29,    // +tgt: controlled (register / thread / tile controls)
+    DC_PERMX = 33,           // +tgt
+    DC_MPHASE = 37,
 };
 #define NONE16 0xFFFFu
 #define NONE32 0xFFFFFFFFu
@@ -84,9 +86,26 @@ struct __align__(16) SwOp {  // 96 bytes = 6 x 16 B, read into registers with si
             uint8_t abit[RB];        // register bit index of each listed slot
             uint8_t n_active;
         } tw;
+        struct {                     // OP_FSTAGE: the first 33 bytes are laid out exactly like `tw`
+            double scale;
+            uint16_t tslot[RB + 1];
+            uint16_t gslot[RB + 1];
+            uint8_t abit[RB];
+            uint8_t n_active;
+            uint8_t hmask;           // @33: number of butterflies NH: register bits 3, 2, ... (3 - NH + 1) get one, in that order
+            uint8_t flags;           // @34: 1 = per-bit deferred phases, 2 = thread-wide factor / scale, 4 = that factor is complex
+            uint8_t pad_;
+            uint16_t w_off[3];       // @36: 16-entry phase table applied right after the butterfly of bit 3 / 2 / 1 (always valid in
+                                     //      the shapes with tables); it touches only registers with bit A set, indexed by the bits below A
+            uint8_t rpos[RB];        // @42: local bit positions of the register bits, ascending (for the thread-index expansion)
+            uint16_t boff[RB];       // @46: swizzled shared-memory slot offset of register bit q (register bits are NOT in position order)
+        } fs;
     };
 };
 static_assert(sizeof(SwOp) == 96, "SwOp layout");
+static_assert(offsetof(SwOp, tw) == 24 && offsetof(SwOp, fs.hmask) == 24 + 33 && offsetof(SwOp, fs.w_off) == 24 + 36 &&
+                  offsetof(SwOp, fs.rpos) == 24 + 42 && offsetof(SwOp, fs.boff) == 24 + 46 && offsetof(SwOp, tw.abit) == offsetof(SwOp, fs.abit),
+              "OP_FSTAGE payload offsets are hard-coded in the kernel");
 
 struct SegMap {  // x -> sum_s ((x >> src) & ((1<<len)-1)) << dst
     uint8_t n, src[MAX_SEG], len[MAX_SEG], dst[MAX_SEG];
@@ -127,17 +146,17 @@ struct SweepParams {
 };
 static_assert(sizeof(SweepParams) < 32700, "kernel parameter space");
 
-__device__ __forceinline__ uint32_t seg_apply(uint32_t x, const SegMap& m) {
+__host__ __device__ __forceinline__ uint32_t seg_apply(uint32_t x, const SegMap& m) {
     uint32_t r = 0;
     for (int s = 0; s < m.n; ++s) r |= ((x >> m.src[s]) & ((1u << m.len[s]) - 1u)) << m.dst[s];
     return r;
 }
-__device__ __forceinline__ uint64_t seg_apply64(uint32_t x, const SegMap& m) {
+__host__ __device__ __forceinline__ uint64_t seg_apply64(uint32_t x, const SegMap& m) {
     uint64_t r = 0;
     for (int s = 0; s < m.n; ++s) r |= (uint64_t)((x >> m.src[s]) & ((1u << m.len[s]) - 1u)) << m.dst[s];
     return r;
 }
-__device__ __forceinline__ uint64_t seg_apply64x(uint64_t x, const SegMap64& m) {
+__host__ __device__ __forceinline__ uint64_t seg_apply64x(uint64_t x, const SegMap64& m) {
     uint64_t r = 0;
     for (int s = 0; s < m.n; ++s) r |= ((x >> m.src[s]) & ((1ull << m.len[s]) - 1ull)) << m.dst[s];
     return r;
@@ -149,27 +168,31 @@ struct OpR {
     uint32_t w0, w1;       // w0 = type | tgt<<8 | rmask<<16 | rval<<24 ; w1 = lmask | lval<<16
     uint64_t gmask, gval;
     uint64_t p[8];         // payload: matrix doubles / stage table / run slots
-    __device__ __forceinline__ uint32_t type() const { return w0 & 0xFFu; }
-    __device__ __forceinline__ uint32_t tgt() const { return (w0 >> 8) & 0xFFu; }
-    __device__ __forceinline__ uint32_t rmask() const { return (w0 >> 16) & 0xFFu; }
-    __device__ __forceinline__ uint32_t rval() const { return w0 >> 24; }
-    __device__ __forceinline__ uint32_t lmask() const { return w1 & 0xFFFFu; }
-    __device__ __forceinline__ uint32_t lval() const { return w1 >> 16; }
-    __device__ __forceinline__ double m(int i) const { return __longlong_as_double((long long)p[i]); }
+    __host__ __device__ __forceinline__ uint32_t type() const { return w0 & 0xFFu; }
+    __host__ __device__ __forceinline__ uint32_t tgt() const { return (w0 >> 8) & 0xFFu; }
+    __host__ __device__ __forceinline__ uint32_t rmask() const { return (w0 >> 16) & 0xFFu; }
+    __host__ __device__ __forceinline__ uint32_t rval() const { return w0 >> 24; }
+    __host__ __device__ __forceinline__ uint32_t lmask() const { return w1 & 0xFFFFu; }
+    __host__ __device__ __forceinline__ uint32_t lval() const { return w1 >> 16; }
+    __host__ __device__ __forceinline__ double m(int i) const {
+        double d;
+        memcpy(&d, &p[i], sizeof(d));  // (bit cast; compiles to nothing on the device)
+        return d;
+    }
     // OP_STAGE payload: roffsw[16] (u16) then rpos[4] (u8)
-    __device__ __forceinline__ uint32_t roffsw(int j) const { return (uint32_t)(p[j >> 2] >> (16 * (j & 3))) & 0xFFFFu; }
-    __device__ __forceinline__ uint32_t rpos(int q) const { return (uint32_t)(p[4] >> (8 * q)) & 0xFFu; }
+    __host__ __device__ __forceinline__ uint32_t roffsw(int j) const { return (uint32_t)(p[j >> 2] >> (16 * (j & 3))) & 0xFFFFu; }
+    __host__ __device__ __forceinline__ uint32_t rpos(int q) const { return (uint32_t)(p[4] >> (8 * q)) & 0xFFu; }
     // generic little-endian field access into the payload (offsets are compile-time constants)
-    __device__ __forceinline__ uint32_t u16_at(int off) const { return (uint32_t)(p[off >> 3] >> (8 * (off & 7))) & 0xFFFFu; }
-    __device__ __forceinline__ uint32_t u8_at(int off) const { return (uint32_t)(p[off >> 3] >> (8 * (off & 7))) & 0xFFu; }
+    __host__ __device__ __forceinline__ uint32_t u16_at(int off) const { return (uint32_t)(p[off >> 3] >> (8 * (off & 7))) & 0xFFFFu; }
+    __host__ __device__ __forceinline__ uint32_t u8_at(int off) const { return (uint32_t)(p[off >> 3] >> (8 * (off & 7))) & 0xFFu; }
     // OP_W payload: w_off @0, wmask @2.  OP_TWID payload: scale @0, tslot[s] @8+2s, gslot[s] @8+2(RB+1)+2s, abit[s] @8+4(RB+1)+s, n_active after
-    __device__ __forceinline__ uint32_t tw_tslot(int s_) const { return u16_at(8 + 2 * s_); }
-    __device__ __forceinline__ uint32_t tw_gslot(int s_) const { return u16_at(8 + 2 * (RB + 1) + 2 * s_); }
-    __device__ __forceinline__ uint32_t tw_abit(int s_) const { return u8_at(8 + 4 * (RB + 1) + s_); }
-    __device__ __forceinline__ uint32_t tw_n() const { return u8_at(8 + 4 * (RB + 1) + RB); }
+    __host__ __device__ __forceinline__ uint32_t tw_tslot(int s_) const { return u16_at(8 + 2 * s_); }
+    __host__ __device__ __forceinline__ uint32_t tw_gslot(int s_) const { return u16_at(8 + 2 * (RB + 1) + 2 * s_); }
+    __host__ __device__ __forceinline__ uint32_t tw_abit(int s_) const { return u8_at(8 + 4 * (RB + 1) + s_); }
+    __host__ __device__ __forceinline__ uint32_t tw_n() const { return u8_at(8 + 4 * (RB + 1) + RB); }
 };
 
-__device__ __forceinline__ OpR fetch_op(const SwOp* __restrict__ ops, int i) {
+__host__ __device__ __forceinline__ OpR fetch_op(const SwOp* __restrict__ ops, int i) {
     const ulonglong2* w = reinterpret_cast<const ulonglong2*>(ops + i);
     const ulonglong2 a = w[0], b = w[1], c = w[2], d = w[3], e = w[4], f = w[5];
     OpR r;
@@ -182,7 +205,7 @@ __device__ __forceinline__ OpR fetch_op(const SwOp* __restrict__ ops, int i) {
 }
 
 template <typename C, bool CTRL, int A>
-__device__ __forceinline__ void op_dense(C (&v)[NREG], const OpR& op, bool tpred) {
+__host__ __device__ __forceinline__ void op_dense(C (&v)[NREG], const OpR& op, bool tpred) {
     typedef decltype(v[0].x) R;
     const C m00 = cmake<C, R>((R)op.m(0), (R)op.m(1)), m01 = cmake<C, R>((R)op.m(2), (R)op.m(3));
     const C m10 = cmake<C, R>((R)op.m(4), (R)op.m(5)), m11 = cmake<C, R>((R)op.m(6), (R)op.m(7));
@@ -201,7 +224,7 @@ __device__ __forceinline__ void op_dense(C (&v)[NREG], const OpR& op, bool tpred
 
 // real-entry matrices (H, rotations about y, ...): half the multiplies
 template <typename C, bool CTRL, int A>
-__device__ __forceinline__ void op_dense_real(C (&v)[NREG], const OpR& op, bool tpred) {
+__host__ __device__ __forceinline__ void op_dense_real(C (&v)[NREG], const OpR& op, bool tpred) {
     typedef decltype(v[0].x) R;
     const R m00 = (R)op.m(0), m01 = (R)op.m(2), m10 = (R)op.m(4), m11 = (R)op.m(6);
     const uint32_t rm = op.rmask(), rv = op.rval();
@@ -220,7 +243,7 @@ __device__ __forceinline__ void op_dense_real(C (&v)[NREG], const OpR& op, bool 
 }
 
 template <typename C, int A>
-__device__ __forceinline__ void op_permx(C (&v)[NREG], const OpR& op, bool tpred) {
+__host__ __device__ __forceinline__ void op_permx(C (&v)[NREG], const OpR& op, bool tpred) {
     const uint32_t rm = op.rmask(), rv = op.rval();
 #pragma unroll
     for (int j0 = 0; j0 < NREG; ++j0)
@@ -234,7 +257,7 @@ __device__ __forceinline__ void op_permx(C (&v)[NREG], const OpR& op, bool tpred
         }
 }
 
-__device__ __forceinline__ uint32_t expand_rb(uint32_t g, const uint8_t* rpos) {
+__host__ __device__ __forceinline__ uint32_t expand_rb(uint32_t g, const uint8_t* rpos) {
 #pragma unroll
     for (int q = 0; q < RB; ++q) {
         const uint32_t p = rpos[q];
@@ -245,7 +268,7 @@ __device__ __forceinline__ uint32_t expand_rb(uint32_t g, const uint8_t* rpos) {
 
 // unnormalised Hadamard butterfly on register bit A: (a0, a1) -> (a0 + a1, a0 - a1)
 template <typename C, int A>
-__device__ __forceinline__ void op_hadd(C (&v)[NREG]) {
+__host__ __device__ __forceinline__ void op_hadd(C (&v)[NREG]) {
 #pragma unroll
     for (int j0 = 0; j0 < NREG; ++j0)
         if (!(j0 & (1 << A))) {
@@ -260,12 +283,238 @@ __device__ __forceinline__ void op_hadd(C (&v)[NREG]) {
 
 // v[j] *= e for every register j that has bit A set
 template <typename C, int A>
-__device__ __forceinline__ void mul_bit(C (&v)[NREG], const double2 e) {
+__host__ __device__ __forceinline__ void mul_bit(C (&v)[NREG], const double2 e) {
     typedef decltype(v[0].x) R;
     const C ee = cmake<C, R>((R)e.x, (R)e.y);
 #pragma unroll
     for (int j = 0; j < NREG; ++j)
         if (j & (1 << A)) v[j] = cmul(v[j], ee);
+}
+
+// Deferred phases of a stage (OP_TWID and the tail of OP_FSTAGE): thread-wide complex factor / real scale, then one factor per
+// register bit -- each the product of a per-tile scalar (smE) and two 16-entry tables over the 4-bit chunks of the thread id.
+template <typename C, typename R>
+__host__ __device__ __forceinline__ void twid_math(C (&v)[NREG], const OpR& op, const double2* __restrict__ smT, const double2* __restrict__ smE,
+                                          const uint32_t tid) {
+    const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
+    const double scale = op.m(0);
+    const uint32_t ts0 = op.tw_tslot(RB), gs0 = op.tw_gslot(RB);
+    if (ts0 != NONE16 || gs0 != NONE16) {  // thread-wide complex factor (times the scale)
+        double2 c0 = make_double2(scale, 0.0);
+        if (gs0 != NONE16) {
+            const double2 g0 = smE[gs0];
+            c0 = make_double2(scale * g0.x, scale * g0.y);
+        }
+        if (ts0 != NONE16) c0 = cmul(c0, cmul(smT[ts0 + c_lo], smT[ts0 + c_hi]));
+        const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
+#pragma unroll
+        for (int j = 0; j < NREG; ++j) v[j] = cmul(v[j], cc);
+    } else if (scale != 1.0) {
+        const R sc = (R)scale;
+#pragma unroll
+        for (int j = 0; j < NREG; ++j) {
+            v[j].x *= sc;
+            v[j].y *= sc;
+        }
+    }
+    // slot s_ holds the factor of register bit s_ (abit[s_] == 0xFF: nothing pending on that bit)
+#define TWID_BIT(B)                                                             \
+    if (op.tw_abit(B) != 0xFFu) {                                               \
+        double2 e = make_double2(1.0, 0.0);                                     \
+        const uint32_t gsl = op.tw_gslot(B), tsl = op.tw_tslot(B);              \
+        if (gsl != NONE16) e = smE[gsl];                                        \
+        if (tsl != NONE16) e = cmul(e, cmul(smT[tsl + c_lo], smT[tsl + c_hi])); \
+        mul_bit<C, B>(v, e);                                                    \
+    }
+    TWID_BIT(0)
+    TWID_BIT(1)
+    TWID_BIT(2)
+    TWID_BIT(3)
+#undef TWID_BIT
+}
+
+// OP_FSTAGE arithmetic, one straight line per SHAPE so that no branch ever joins two register allocations:
+//   NH    butterflies on the TOP NH register bits, in the order 3, 2, ... (the host relabels register bits to make it so);
+//   HAS_W each butterfly on bit A > 0 is followed by its register-register phase table, which multiplies only registers
+//         with bit A set and depends only on the register bits below A (the internal twiddles of a radix-16 FFT
+//         butterfly): 7 + 2*3 + 4*1 multiplies, statically indexed (absent tables point at an all-ones table);
+//   then the deferred phases: unconditionally on the NH butterfly bits (absent factors point at all-ones slots),
+//   behind a uniform branch for the thread-wide factor / scale and for the other register bits (rare).
+template <typename C, typename R, int B>
+__host__ __device__ __forceinline__ void twid_bit_always(C (&v)[NREG], const OpR& op, const double2* __restrict__ smT, const double2* __restrict__ smE,
+                                                const uint32_t c_lo, const uint32_t c_hi) {
+    const uint32_t gsl = op.tw_gslot(B), tsl = op.tw_tslot(B);
+    const double2 e = cmul(smE[gsl], cmul(smT[tsl + c_lo], smT[tsl + c_hi]));
+    mul_bit<C, B>(v, e);
+}
+template <typename C, typename R, int B>
+__host__ __device__ __forceinline__ void twid_bit_maybe(C (&v)[NREG], const OpR& op, const double2* __restrict__ smT, const double2* __restrict__ smE,
+                                               const uint32_t c_lo, const uint32_t c_hi) {
+    if (op.tw_abit(B) != 0xFFu) twid_bit_always<C, R, B>(v, op, smT, smE, c_lo, c_hi);
+}
+
+template <typename C, typename R, int NH, bool HAS_W>
+__host__ __device__ __forceinline__ void fstage_math(C (&v)[NREG], const OpR& op, const double2* __restrict__ smT, const double2* __restrict__ smE,
+                                            const uint32_t tid) {
+    if constexpr (NH >= 1) {
+        op_hadd<C, 3>(v);
+        if constexpr (HAS_W) {
+            const double2* w = smT + op.u16_at(36) + 8;
+#pragma unroll
+            for (int m = 1; m < 8; ++m) {
+                const double2 e = w[m];
+                v[8 + m] = cmul(v[8 + m], cmake<C, R>((R)e.x, (R)e.y));
+            }
+        }
+    }
+    if constexpr (NH >= 2) {
+        op_hadd<C, 2>(v);
+        if constexpr (HAS_W) {
+            const double2* w = smT + op.u16_at(38) + 4;
+#pragma unroll
+            for (int m = 1; m < 4; ++m) {
+                const double2 e = w[m];
+                const C ee = cmake<C, R>((R)e.x, (R)e.y);
+                v[4 + m] = cmul(v[4 + m], ee);
+                v[12 + m] = cmul(v[12 + m], ee);
+            }
+        }
+    }
+    if constexpr (NH >= 3) {
+        op_hadd<C, 1>(v);
+        if constexpr (HAS_W) {
+            const double2 e = smT[op.u16_at(40) + 3];
+            const C ee = cmake<C, R>((R)e.x, (R)e.y);
+            v[3] = cmul(v[3], ee);
+            v[7] = cmul(v[7], ee);
+            v[11] = cmul(v[11], ee);
+            v[15] = cmul(v[15], ee);
+        }
+    }
+    if constexpr (NH >= 4) op_hadd<C, 0>(v);
+    // ---- deferred phases ----
+    const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
+    const uint32_t fl = op.u8_at(34);
+    if (fl & 2u) {  // thread-wide complex factor and / or real scale
+        const double scale = op.m(0);
+        const uint32_t ts0 = op.tw_tslot(RB), gs0 = op.tw_gslot(RB);
+        if (fl & 4u) {
+            const double2 g0 = smE[gs0];
+            const double2 c0 = cmul(make_double2(scale * g0.x, scale * g0.y), cmul(smT[ts0 + c_lo], smT[ts0 + c_hi]));
+            const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
+#pragma unroll
+            for (int j = 0; j < NREG; ++j) v[j] = cmul(v[j], cc);
+        } else {
+            const R sc = (R)scale;
+#pragma unroll
+            for (int j = 0; j < NREG; ++j) {
+                v[j].x *= sc;
+                v[j].y *= sc;
+            }
+        }
+    }
+    if (fl & 1u) {
+        if constexpr (NH >= 1) twid_bit_always<C, R, 3>(v, op, smT, smE, c_lo, c_hi); else twid_bit_maybe<C, R, 3>(v, op, smT, smE, c_lo, c_hi);
+        if constexpr (NH >= 2) twid_bit_always<C, R, 2>(v, op, smT, smE, c_lo, c_hi); else twid_bit_maybe<C, R, 2>(v, op, smT, smE, c_lo, c_hi);
+        if constexpr (NH >= 3) twid_bit_always<C, R, 1>(v, op, smT, smE, c_lo, c_hi); else twid_bit_maybe<C, R, 1>(v, op, smT, smE, c_lo, c_hi);
+        if constexpr (NH >= 4) twid_bit_always<C, R, 0>(v, op, smT, smE, c_lo, c_hi); else twid_bit_maybe<C, R, 0>(v, op, smT, smE, c_lo, c_hi);
+    }
+}
+
+// One whole OP_FSTAGE: shared memory -> registers -> fstage_math -> shared memory, or straight to HBM when this is the
+// launch's last op and the stage's register bits allow a coalesced store.  Returns true when it stored to HBM.
+template <typename C, typename R, int NH, bool HAS_W>
+__host__ __device__ __forceinline__ bool fstage_op(const OpR& op, C* __restrict__ tile, const double2* __restrict__ smT,
+                                          const double2* __restrict__ smE, const uint32_t tid, const bool active, const bool to_hbm,
+                                          C* __restrict__ dst, const uint64_t gbs, const uint64_t (&st_goff)[NREG]) {
+    // (threads beyond the tile's groups -- tiles smaller than a warp's worth -- redo thread 0's loads and never store:
+    // an unconditional load keeps the registers defined on every path, which the register allocator needs)
+    uint32_t bl = active ? tid : 0u;
+#pragma unroll
+    for (int q = 0; q < RB; ++q) {
+        const uint32_t pz = op.u8_at(42 + q);
+        bl = ((bl >> pz) << (pz + 1)) | (bl & ((1u << pz) - 1u));
+    }
+    // swizzle and register offsets are XOR-linear: slot of register j = slot of register 0 ^ offsets of j's set bits
+    uint32_t a[NREG];
+    a[0] = swz(bl);
+#pragma unroll
+    for (int j = 1; j < NREG; ++j) a[j] = a[j & (j - 1)] ^ op.u16_at(46 + 2 * ((j & 1) ? 0 : (j & 2) ? 1 : (j & 4) ? 2 : 3));
+    C w[NREG];
+#pragma unroll
+    for (int j = 0; j < NREG; ++j) w[j] = tile[a[j]];
+    fstage_math<C, R, NH, HAS_W>(w, op, smT, smE, tid);
+    if (to_hbm) {
+        if (active) {
+#pragma unroll
+            for (int j = 0; j < NREG; ++j) dst[gbs | st_goff[j]] = w[j];
+        }
+        return true;
+    }
+    if (active) {
+#pragma unroll
+        for (int j = 0; j < NREG; ++j) tile[a[j]] = w[j];
+    }
+#ifdef __CUDA_ARCH__
+    __syncthreads();
+#endif
+    return false;
+}
+
+// One op of the generic interpreter applied to a thread's 16 registers (everything but the stage changes).
+template <typename C, typename R, bool LEAN>
+__host__ __device__ __forceinline__ void generic_op(C (&v)[NREG], const OpR& op, const uint32_t type, const bool tpred,
+                                                    const double2* __restrict__ smT, const double2* __restrict__ smE, const uint32_t tid) {
+#define DENSE_CASES(BASE, FN, CTRL)                                   \
+    case BASE + 0: FN<C, CTRL, 0>(v, op, tpred); break;               \
+    case BASE + 1: FN<C, CTRL, 1>(v, op, tpred); break;               \
+    case BASE + 2: FN<C, CTRL, 2>(v, op, tpred); break;               \
+    case BASE + 3: FN<C, CTRL, 3>(v, op, tpred); break;
+    switch (type) {
+        DENSE_CASES(DC_DENSE_REAL_NC, op_dense_real, false)
+        DENSE_CASES(DC_DENSE_CPLX_NC, op_dense, false)
+        case DC_DENSE_CPLX_C + 0: if constexpr (!LEAN) op_dense<C, true, 0>(v, op, tpred); break;
+        case DC_DENSE_CPLX_C + 1: if constexpr (!LEAN) op_dense<C, true, 1>(v, op, tpred); break;
+        case DC_DENSE_CPLX_C + 2: if constexpr (!LEAN) op_dense<C, true, 2>(v, op, tpred); break;
+        case DC_DENSE_CPLX_C + 3: if constexpr (!LEAN) op_dense<C, true, 3>(v, op, tpred); break;
+        case DC_PERMX + 0: if constexpr (!LEAN) op_permx<C, 0>(v, op, tpred); break;
+        case DC_PERMX + 1: if constexpr (!LEAN) op_permx<C, 1>(v, op, tpred); break;
+        case DC_PERMX + 2: if constexpr (!LEAN) op_permx<C, 2>(v, op, tpred); break;
+        case DC_PERMX + 3: if constexpr (!LEAN) op_permx<C, 3>(v, op, tpred); break;
+        case DC_MPHASE: {
+            if constexpr (!LEAN) {
+                const C d = cmake<C, R>((R)op.m(0), (R)op.m(1));
+                const uint32_t rm = op.rmask(), rv = op.rval();
+#pragma unroll
+                for (int j = 0; j < NREG; ++j)
+                    if (((j & rm) == rv) && tpred) v[j] = cmul(v[j], d);
+            }
+            break;
+        }
+        case DC_HADD + 0: op_hadd<C, 0>(v); break;
+        case DC_HADD + 1: op_hadd<C, 1>(v); break;
+        case DC_HADD + 2: op_hadd<C, 2>(v); break;
+        case DC_HADD + 3: op_hadd<C, 3>(v); break;
+#define APPLY_W()                                                              \
+    {                                                                          \
+const double2* w = smT + op.u16_at(0);                                 \
+const uint32_t wm = op.u16_at(2);                                      \
+_Pragma("unroll") for (int j = 0; j < NREG; ++j) if ((wm >> j) & 1) {  \
+    const double2 ww = w[j];                                           \
+    v[j] = cmul(v[j], cmake<C, R>((R)ww.x, (R)ww.y));                  \
+}                                                                      \
+    }
+        case DC_W: APPLY_W() break;
+        case DC_HW + 0: op_hadd<C, 0>(v); APPLY_W() break;
+        case DC_HW + 1: op_hadd<C, 1>(v); APPLY_W() break;
+        case DC_HW + 2: op_hadd<C, 2>(v); APPLY_W() break;
+        case DC_HW + 3: op_hadd<C, 3>(v); APPLY_W() break;
+#undef APPLY_W
+        case DC_TWID: twid_math<C, R>(v, op, smT, smE, tid); break;
+        default:
+            break;
+    }
+#undef DENSE_CASES
 }
 
 template <int BYTES>
@@ -281,14 +530,21 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 
 // Two instantiations: <256, 1> for 64 KB tiles (k = 12, one CTA per SM) and <128, 3> for smaller tiles
 // (register cap 168 so that three double-buffered 32 KB-tile CTAs share an SM).
-// LEAN = the op set of Hadamard/phase circuits only (stage, uncontrolled dense, unnormalised butterfly, phase tables):
-// a smaller kernel image for the common case; the full image adds controlled dense gates, swaps and masked phases.
-template <typename R, int MAXT, int MINB, bool LEAN>
+// Three images per (dtype, tile size):
+//   IMG_FULL  every op kind;
+//   IMG_LEAN  the op set of Hadamard/phase circuits only (stage, uncontrolled dense, unnormalised butterfly, phase tables);
+//   IMG_FFT   launches made of OP_FSTAGE ops only: no amplitude is carried in registers from one op to the next, so the
+//             op loop has no register-allocation joins (the generic loop spends ~20 % of its instructions on moves there).
+#define IMG_FULL 0
+#define IMG_LEAN 1
+#define IMG_FFT 2
+template <typename R, int MAXT, int MINB, int IMG>
 __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>::type* __restrict__ src,
                                                   typename cplx_of<R>::type* __restrict__ dst,
                                                   const double* __restrict__ aux,
                                                   const __grid_constant__ SweepParams P) {
     typedef typename cplx_of<R>::type C;
+    constexpr bool LEAN = IMG != IMG_FULL;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const SweepDesc& D = P.d;
     const size_t tile_bytes = (size_t)sizeof(C) << D.k;
@@ -344,6 +600,35 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
             cp_async_commit();
         }
 
+        if constexpr (IMG == IMG_FFT) {
+            // every op is a whole stage in one straight line: shared memory -> registers -> butterflies + phases ->
+            // shared memory (or, for the launch's last stage, straight to HBM)
+            bool stored = false;
+            const uint64_t gbs = seg_apply64x(t, D.out_glob) | t_st_g;
+            for (int i = 0; i < D.n_ops; ++i) {
+                const OpR op = fetch_op(P.ops, i);
+                const bool to_hbm = dstore && i == D.n_ops - 1;
+#define FS(NH, HAS_W) stored = fstage_op<C, R, NH, HAS_W>(op, tile, smT, smE, tid, active, to_hbm, dst, gbs, D.st_goff); break;
+                switch (op.type() - DC_FSTAGE) {  // shape = 2 * (number of butterflies) + (phase tables present)
+                    case 0: case 1: FS(0, false)
+                    case 2: FS(1, false)
+                    case 3: FS(1, true)
+                    case 4: FS(2, false)
+                    case 5: FS(2, true)
+                    case 6: FS(3, false)
+                    case 7: FS(3, true)
+                    case 8: FS(4, false)
+                    default: FS(4, true)
+                }
+#undef FS
+            }
+            if (!stored) {
+                const uint64_t gb = gbs;
+#pragma unroll
+                for (int i = 0; i < NREG; ++i)
+                    if (i < n_slots) dst[gb | D.st_goff[i]] = tile[t_st_s ^ D.st_soff[i]];  // (exchange sweeps carry no ops and never use this image)
+            }
+        } else {
         C v[NREG];
         uint32_t base_l = 0, swbase = 0;
         bool have_stage = false;
@@ -383,92 +668,7 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
                 if (op.gmask && (t & op.gmask) != op.gval) continue;  // control on a tile-id bit not satisfied for this tile
                 tpred = (base_l & op.lmask()) == op.lval();
             }
-#define DENSE_CASES(BASE, FN, CTRL)                                   \
-    case BASE + 0: FN<C, CTRL, 0>(v, op, tpred); break;               \
-    case BASE + 1: FN<C, CTRL, 1>(v, op, tpred); break;               \
-    case BASE + 2: FN<C, CTRL, 2>(v, op, tpred); break;               \
-    case BASE + 3: FN<C, CTRL, 3>(v, op, tpred); break;
-            switch (type) {
-                DENSE_CASES(DC_DENSE_REAL_NC, op_dense_real, false)
-                DENSE_CASES(DC_DENSE_CPLX_NC, op_dense, false)
-                case DC_DENSE_CPLX_C + 0: if constexpr (!LEAN) op_dense<C, true, 0>(v, op, tpred); break;
-                case DC_DENSE_CPLX_C + 1: if constexpr (!LEAN) op_dense<C, true, 1>(v, op, tpred); break;
-                case DC_DENSE_CPLX_C + 2: if constexpr (!LEAN) op_dense<C, true, 2>(v, op, tpred); break;
-                case DC_DENSE_CPLX_C + 3: if constexpr (!LEAN) op_dense<C, true, 3>(v, op, tpred); break;
-                case DC_PERMX + 0: if constexpr (!LEAN) op_permx<C, 0>(v, op, tpred); break;
-                case DC_PERMX + 1: if constexpr (!LEAN) op_permx<C, 1>(v, op, tpred); break;
-                case DC_PERMX + 2: if constexpr (!LEAN) op_permx<C, 2>(v, op, tpred); break;
-                case DC_PERMX + 3: if constexpr (!LEAN) op_permx<C, 3>(v, op, tpred); break;
-                case DC_MPHASE: {
-                    if constexpr (!LEAN) {
-                        const C d = cmake<C, R>((R)op.m(0), (R)op.m(1));
-                        const uint32_t rm = op.rmask(), rv = op.rval();
-#pragma unroll
-                        for (int j = 0; j < NREG; ++j)
-                            if (((j & rm) == rv) && tpred) v[j] = cmul(v[j], d);
-                    }
-                    break;
-                }
-                case DC_HADD + 0: op_hadd<C, 0>(v); break;
-                case DC_HADD + 1: op_hadd<C, 1>(v); break;
-                case DC_HADD + 2: op_hadd<C, 2>(v); break;
-                case DC_HADD + 3: op_hadd<C, 3>(v); break;
-#define APPLY_W()                                                              \
-    {                                                                          \
-        const double2* w = smT + op.u16_at(0);                                 \
-        const uint32_t wm = op.u16_at(2);                                      \
-        _Pragma("unroll") for (int j = 0; j < NREG; ++j) if ((wm >> j) & 1) {  \
-            const double2 ww = w[j];                                           \
-            v[j] = cmul(v[j], cmake<C, R>((R)ww.x, (R)ww.y));                  \
-        }                                                                      \
-    }
-                case DC_W: APPLY_W() break;
-                case DC_HW + 0: op_hadd<C, 0>(v); APPLY_W() break;
-                case DC_HW + 1: op_hadd<C, 1>(v); APPLY_W() break;
-                case DC_HW + 2: op_hadd<C, 2>(v); APPLY_W() break;
-                case DC_HW + 3: op_hadd<C, 3>(v); APPLY_W() break;
-#undef APPLY_W
-                case DC_TWID: {
-                    const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
-                    const double scale = op.m(0);
-                    const uint32_t ts0 = op.tw_tslot(RB), gs0 = op.tw_gslot(RB);
-                    if (ts0 != NONE16 || gs0 != NONE16) {  // thread-wide complex factor (times the scale)
-                        double2 c0 = make_double2(scale, 0.0);
-                        if (gs0 != NONE16) {
-                            const double2 g0 = smE[gs0];
-                            c0 = make_double2(scale * g0.x, scale * g0.y);
-                        }
-                        if (ts0 != NONE16) c0 = cmul(c0, cmul(smT[ts0 + c_lo], smT[ts0 + c_hi]));
-                        const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
-#pragma unroll
-                        for (int j = 0; j < NREG; ++j) v[j] = cmul(v[j], cc);
-                    } else if (scale != 1.0) {
-                        const R sc = (R)scale;
-#pragma unroll
-                        for (int j = 0; j < NREG; ++j) {
-                            v[j].x *= sc;
-                            v[j].y *= sc;
-                        }
-                    }
-                    // slot s_ holds the factor of register bit s_ (abit[s_] == 0xFF: nothing pending on that bit)
-#define TWID_BIT(B)                                                                                      \
-    if (op.tw_abit(B) != 0xFFu) {                                                                        \
-        double2 e = make_double2(1.0, 0.0);                                                              \
-        const uint32_t gsl = op.tw_gslot(B), tsl = op.tw_tslot(B);                                       \
-        if (gsl != NONE16) e = smE[gsl];                                                                 \
-        if (tsl != NONE16) e = cmul(e, cmul(smT[tsl + c_lo], smT[tsl + c_hi]));                          \
-        mul_bit<C, B>(v, e);                                                                             \
-    }
-                    TWID_BIT(0)
-                    TWID_BIT(1)
-                    TWID_BIT(2)
-                    TWID_BIT(3)
-#undef TWID_BIT
-                    break;
-                }
-                default:
-                    break;
-            }
+            generic_op<C, R, LEAN>(v, op, type, tpred, smT, smE, tid);
         }
         // ---- store the tile (possibly to a bit-permuted location of the other buffer) ----------
         const uint64_t gb = seg_apply64x(t, D.out_glob) | t_st_g;
@@ -501,6 +701,7 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
                     }
                 }
         }
+        }  // generic images
         __syncthreads();  // this buffer and the per-tile scalars are rewritten two / one tiles from now
         cur ^= 1;
     }
@@ -515,7 +716,7 @@ struct PlanStep {
     size_t gate_index;      // !fused: index into ctx->gates
     SweepParams* params;    // fused (host copy)
     bool out_of_place;
-    bool lean;              // every op is in the lean kernel's set
+    int img;                // kernel image that runs it: IMG_FFT (only OP_FSTAGE ops), IMG_LEAN (lean op set) or IMG_FULL
     uint64_t n_gates;       // source gates carried
 };
 
@@ -1059,6 +1260,173 @@ struct Builder {
             if (std::find(r.begin(), r.end(), l) == r.end()) sc.tloc.push_back(l);
     }
 
+    // Does the 16-entry table at `off` have the shape OP_FSTAGE applies after the butterfly on register bit A: 1 for
+    // registers without bit A, and for the others a value that depends only on the register bits below A?
+    static bool fft_table_shape(const std::vector<double>& tab, size_t off, int A) {
+        for (int j = 0; j < NREG; ++j) {
+            const double re = tab[2 * (off + j)], im = tab[2 * (off + j) + 1];
+            if (!((j >> A) & 1)) {
+                if (re != 1.0 || im != 0.0) return false;
+                continue;
+            }
+            const int m = j & ((1 << A) - 1);
+            if (m == 0) {
+                if (re != 1.0 || im != 0.0) return false;
+                continue;
+            }
+            const size_t r = off + (size_t)((1 << A) | m);
+            if (re != tab[2 * r] || im != tab[2 * r + 1]) return false;
+        }
+        return true;
+    }
+
+    // If every stage of the launch is "FFT shaped" -- butterflies on distinct register bits, each optionally followed by a
+    // phase table that couples it only to bits whose butterfly comes later (or never), and at most one deferred-phase op at
+    // the end -- rewrite each stage (OP_STAGE + its ops) as ONE OP_FSTAGE.  Register bits are relabelled so that the
+    // butterflies run on bits 3, 2, 1, 0 in that order (tables and per-bit slots are permuted to match).  All-or-nothing per
+    // launch: the IMG_FFT kernel image runs only such ops and carries nothing in registers between them.
+    bool to_fstages(Emit& e) {
+        static const bool off = getenv("QSV_NO_FSTAGE") != nullptr;  // debugging / A-B aid
+        static const bool dbg = getenv("QSV_FSTAGE_DEBUG") != nullptr;
+#define FS_NO(why)                                                                  \
+    do {                                                                            \
+        if (dbg) fprintf(stderr, "[qsv] launch stays generic: %s\n", why);          \
+        return false;                                                               \
+    } while (0)
+        if (off || e.ops.empty()) return false;
+        std::vector<double> tab = e.tab;  // tables are permuted on a copy: a failed conversion must leave the launch intact
+        std::vector<std::vector<double>> gslots = e.gslots;
+        int one_g = -1, one_t = -1, one_w = -1;
+        auto ones_gslot = [&]() {
+            if (one_g < 0) {
+                gslots.push_back(std::vector<double>(1 + glob_pos.size(), 0.0));
+                one_g = (int)gslots.size() - 1;
+            }
+            return (uint16_t)one_g;
+        };
+        auto ones_table = [&](int& slot, size_t len) {
+            if (slot < 0) {
+                slot = (int)(tab.size() / 2);
+                for (size_t i = 0; i < len; ++i) {
+                    tab.push_back(1.0);
+                    tab.push_back(0.0);
+                }
+            }
+            return (uint16_t)slot;
+        };
+        std::vector<SwOp> out;
+        std::vector<int> last_order;
+        size_t i = 0;
+        while (i < e.ops.size()) {
+            if (e.ops[i].type != OP_STAGE) FS_NO("does not start with a stage");
+            const SwOp st = e.ops[i++];
+            // ---- pass 1: the stage's ops and the butterfly order
+            std::vector<const SwOp*> body;
+            while (i < e.ops.size() && e.ops[i].type != OP_STAGE) body.push_back(&e.ops[i++]);
+            std::vector<int> order;  // old register bits in butterfly order
+            const SwOp* tw = nullptr;
+            for (const SwOp* o : body) {
+                if (tw) FS_NO("an op follows the deferred phases");
+                if (o->type == OP_HADD || o->type == OP_HW) {
+                    if (std::find(order.begin(), order.end(), (int)o->tgt) != order.end()) FS_NO("two butterflies on one register bit");
+                    order.push_back(o->tgt);
+                } else if (o->type == OP_TWID) {
+                    tw = o;
+                } else {
+                    if (dbg) fprintf(stderr, "[qsv] op kind %d\n", (int)o->type);
+                    FS_NO("an op kind outside the FFT shape");
+                }
+            }
+            const int nh = (int)order.size();
+            for (int q = RB - 1; q >= 0; --q)  // the other register bits keep their relative order below the butterfly bits
+                if (std::find(order.begin(), order.end(), q) == order.end()) order.push_back(q);
+            int newbit[RB];  // old register bit -> new register bit
+            for (int r = 0; r < RB; ++r) newbit[order[r]] = RB - 1 - r;
+            auto map_j = [&](int j) {
+                int r = 0;
+                for (int q = 0; q < RB; ++q)
+                    if ((j >> q) & 1) r |= 1 << newbit[q];
+                return r;
+            };
+            SwOp f;
+            memset(&f, 0, sizeof(f));
+            f.type = OP_FSTAGE;
+            f.fs.scale = 1.0;
+            f.fs.hmask = (uint8_t)nh;
+            for (int s_ = 0; s_ <= RB; ++s_) f.fs.tslot[s_] = f.fs.gslot[s_] = NONE16;
+            for (int q = 0; q < RB; ++q) {
+                f.fs.abit[q] = 0xFF;
+                f.fs.rpos[q] = st.st.rpos[q];
+                f.fs.boff[newbit[q]] = (uint16_t)swz(1u << st.st.rpos[q]);
+            }
+            for (int q = 0; q < 3; ++q) f.fs.w_off[q] = NONE16;
+            // ---- pass 2: tables
+            bool any_w = false;
+            for (const SwOp* o : body) {
+                if (o->type != OP_HW) continue;
+                const int A = newbit[o->tgt];
+                double perm[2 * NREG];
+                for (int j = 0; j < NREG; ++j) {
+                    perm[2 * map_j(j)] = tab[2 * (o->w.w_off + j)];
+                    perm[2 * map_j(j) + 1] = tab[2 * (o->w.w_off + j) + 1];
+                }
+                memcpy(&tab[2 * o->w.w_off], perm, sizeof(perm));
+                if (!fft_table_shape(tab, o->w.w_off, A)) FS_NO("a phase table couples bits outside the FFT shape");
+                if (A > 0 && o->w.wmask) {
+                    f.fs.w_off[3 - A] = o->w.w_off;
+                    any_w = true;
+                }
+            }
+            if (any_w)
+                for (int q = 0; q < 3; ++q)
+                    if (f.fs.w_off[q] == NONE16) f.fs.w_off[q] = ones_table(one_w, NREG);
+            // ---- deferred phases
+            if (tw) {
+                f.fs.scale = tw->tw.scale;
+                bool any_bit = false;
+                for (int q = 0; q < RB; ++q)
+                    if (tw->tw.abit[q] != 0xFF) {
+                        const int nq = newbit[q];
+                        f.fs.abit[nq] = (uint8_t)nq;
+                        f.fs.tslot[nq] = tw->tw.tslot[q];
+                        f.fs.gslot[nq] = tw->tw.gslot[q];
+                        any_bit = true;
+                    }
+                f.fs.n_active = tw->tw.n_active;
+                f.fs.tslot[RB] = tw->tw.tslot[RB];
+                f.fs.gslot[RB] = tw->tw.gslot[RB];
+                const bool c0 = f.fs.tslot[RB] != NONE16 || f.fs.gslot[RB] != NONE16;
+                if (any_bit) f.fs.flags |= 1;
+                if (c0 || f.fs.scale != 1.0) f.fs.flags |= 2;
+                if (c0) f.fs.flags |= 4;
+                // every factor the kernel reads unconditionally must point somewhere: absent ones at all-ones slots
+                for (int nq = 0; nq <= RB; ++nq) {
+                    const bool used = nq == RB ? c0 : (any_bit && (f.fs.abit[nq] != 0xFF || nq >= RB - nh));
+                    if (!used) continue;
+                    if (f.fs.tslot[nq] == NONE16) f.fs.tslot[nq] = ones_table(one_t, TSLOT_LEN);
+                    if (f.fs.gslot[nq] == NONE16) f.fs.gslot[nq] = ones_gslot();
+                }
+                for (int nq = RB - nh; nq < RB; ++nq)
+                    if (any_bit) f.fs.abit[nq] = (uint8_t)nq;
+            }
+            f.tgt = (uint8_t)(2 * nh + (any_w ? 1 : 0));  // shape code (added to DC_FSTAGE at conversion)
+            out.push_back(f);
+            last_order = order;
+        }
+        if (gslots.size() > MAX_GSLOT || tab.size() / 2 > MAX_TAB) FS_NO("no room for the all-ones slots");
+#undef FS_NO
+        e.ops.swap(out);
+        e.tab.swap(tab);
+        e.gslots.swap(gslots);
+        // the direct store enumerates the last stage's register bits by (new) register index
+        if (!e.last_rloc.empty()) {
+            std::vector<int> r(RB);
+            for (int rnk = 0; rnk < RB; ++rnk) r[RB - 1 - rnk] = e.last_rloc[last_order[rnk]];
+            e.last_rloc = r;
+        }
+        return true;
+    }
+
     int push_sweep(Emit& e, bool out_of_place, const std::vector<int>* out_pos_of_phys) {
         const bool has_work = std::any_of(e.ops.begin(), e.ops.end(), [](const SwOp& o) { return o.type != OP_STAGE; });
         if (!has_work && !out_of_place) {
@@ -1070,6 +1438,7 @@ struct Builder {
         if (e.ops.size() > MAX_OPS || e.gslots.size() > MAX_GSLOT || e.tab.size() / 2 > MAX_TAB)
             return qsv_fail(ctx, QSV_E_TOOBIG, "internal: sweep budget exceeded (%zu ops, %zu slots, %zu table entries)", e.ops.size(),
                             e.gslots.size(), e.tab.size() / 2);
+        const bool all_fft = has_work && to_fstages(e);
         SweepParams* sp = new SweepParams();
         memset(sp, 0, sizeof(*sp));
         SweepDesc& D = sp->d;
@@ -1111,13 +1480,17 @@ struct Builder {
         D.tb = std::max(5, k - RB);
         // direct global <-> register paths: need full tiles (k >= 9) and a stage whose register bits
         // leave the lowest local bits to the lanes, so that the accesses stay coalesced
-        auto high_only = [](const std::vector<int>& r) { return !r.empty() && r[0] >= 4; };
+        auto high_only = [](const std::vector<int>& r) { return !r.empty() && *std::min_element(r.begin(), r.end()) >= 4; };
         static const bool no_direct = getenv("QSV_NO_DIRECT") != nullptr;  // debugging aid
         D.direct_load = 0;  // (loads always go through the cp.async double buffer)
         D.direct_store = !no_direct && has_work && k >= 9 && !out_of_place && high_only(e.last_rloc);
-        for (int q = 0; q < RB; ++q) {
-            D.first_rpos[q] = (uint8_t)(e.first_rloc.empty() ? q : e.first_rloc[q]);
-            D.last_rpos[q] = (uint8_t)(e.last_rloc.empty() ? q : e.last_rloc[q]);
+        {
+            std::vector<int> lr = e.last_rloc;  // (register order of an OP_FSTAGE stage is not position order)
+            std::sort(lr.begin(), lr.end());
+            for (int q = 0; q < RB; ++q) {
+                D.first_rpos[q] = (uint8_t)(e.first_rloc.empty() ? q : e.first_rloc[q]);
+                D.last_rpos[q] = (uint8_t)(lr.empty() ? q : lr[q]);
+            }
         }
         auto dep = [&](uint32_t l, const std::vector<int>& dstpos) {
             uint64_t g = 0;
@@ -1180,6 +1553,7 @@ struct Builder {
                 case OP_HADD: o.type = (uint8_t)(DC_HADD + o.tgt); break;
                 case OP_HW: o.type = (uint8_t)(DC_HW + o.tgt); break;
                 case OP_W: o.type = DC_W; break;
+                case OP_FSTAGE: o.type = (uint8_t)(DC_FSTAGE + o.tgt); break;
                 default: o.type = DC_TWID; break;
             }
             sp->ops[i] = o;
@@ -1190,7 +1564,7 @@ struct Builder {
         s.fused = true;
         s.params = sp;
         s.out_of_place = out_of_place;
-        s.lean = all_lean;
+        s.img = all_fft ? IMG_FFT : all_lean ? IMG_LEAN : IMG_FULL;
         s.n_gates = e.n_gates;
         plan->steps.push_back(s);
         e = Emit();
@@ -1264,7 +1638,7 @@ struct Builder {
             };
             int n_plain_h = 0;
             for (size_t q = i; q < j; ++q) n_plain_h += is_plain_h(pg[cur[q]]);
-            const bool hadd_mode = n_plain_h >= 2;
+            const bool hadd_mode = n_plain_h >= 1;  // (a single one costs the same either way, and keeps the stage FFT-shaped)
             std::vector<size_t> run;
             const size_t RUN_CHUNK = 64;
             for (size_t q = i; q < j; ++q) {
@@ -1311,15 +1685,12 @@ struct Builder {
                 run.clear();
                 // stage end: everything deferred must land before the register bits change; the owed scale
                 // rides along if this is the sweep's last stage
-                rc = flush_pending(e, sc, (1u << RB) - 1u, j >= cur.size());
+                const bool last_stage = j >= cur.size();
+                const double keep = sweep_scale;
+                if (!last_stage) sweep_scale = 1.0;  // (the thread-wide factor is applied per stage, the scale once per sweep)
+                rc = flush_pending(e, sc, (1u << RB) - 1u, true);
+                if (!last_stage) sweep_scale = keep;
                 if (rc) return rc;
-                if (pend.c0.any) {  // thread-wide factor still pending (not the last stage): apply it now as well
-                    const double keep = sweep_scale;
-                    sweep_scale = 1.0;
-                    rc = flush_pending(e, sc, 0, true);
-                    sweep_scale = keep;
-                    if (rc) return rc;
-                }
             }
             i = j;
         }
@@ -1335,7 +1706,8 @@ struct Builder {
 
 static int sweep_set_smem_attr(qsv_ctx* ctx, int k);
 
-int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
+// host-only part of the fusion pass: no CUDA call, usable without a device (qsv_hostcheck_fused)
+static int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan) {
     const int n = ctx->prog_bits;
     if (n < RB) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "unsupported: fused sweeps need at least %d index bits (have %d)", RB, n);
     // default tile: the whole state when it fits, else 2^11 amplitudes (32 KB): measured best on B200 -- three
@@ -1367,6 +1739,17 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
         return rc;
     }
     plan->dropped_identities += b.relabelled_gates;  // counted as applied source gates
+    *out_plan = plan;
+    return QSV_OK;
+}
+
+int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
+    SweepPlan* plan = nullptr;
+    {
+        int rc = sweep_plan_build_host(ctx, max_tile_bits, &plan);
+        if (rc) return rc;
+    }
+    const int k = plan->k;
     cudaError_t e = cudaMalloc(&plan->d_aux, plan->aux.size() * sizeof(double));
     if (e == cudaSuccess) e = cudaMemcpy(plan->d_aux, plan->aux.data(), plan->aux.size() * sizeof(double), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) {
@@ -1393,52 +1776,51 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
 // defined in qsv.cu
 int qsv_apply_planned_single(qsv_ctx* ctx, void* state, size_t gate_index, cudaStream_t s);
 
-template <typename R, int MAXT, int MINB, bool LEAN>
+template <typename R, int MAXT, int MINB, int IMG>
 static cudaError_t sweep_image_launch(bool set_attr_only, int* occ_out, unsigned grid, int threads, size_t smem, cudaStream_t stream,
                                       const void* src, void* dst, const double* d_aux, const SweepParams* params) {
     typedef typename cplx_of<R>::type C;
-    auto kern = k_sweep<R, MAXT, MINB, LEAN>;
+    auto kern = k_sweep<R, MAXT, MINB, IMG>;
     if (set_attr_only) return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (occ_out) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ_out, kern, threads, smem);
     kern<<<grid, threads, smem, stream>>>((const C*)src, (C*)dst, d_aux, *params);
     return cudaGetLastError();
 }
 
-// picks the kernel image for (dtype, tile size, lean) and either sets its smem attribute, queries occupancy or launches it
-static cudaError_t sweep_image(qsv_ctx* ctx, int k, bool lean, bool set_attr_only, int* occ_out, unsigned grid, int threads, size_t smem,
+// picks the kernel image for (dtype, tile size, image kind) and either sets its smem attribute, queries occupancy or launches it
+static cudaError_t sweep_image(qsv_ctx* ctx, int k, int img, bool set_attr_only, int* occ_out, unsigned grid, int threads, size_t smem,
                                cudaStream_t stream, const void* src, void* dst, const double* d_aux, const SweepParams* params) {
-#define IMG(R, MAXT, MINB, LEAN) sweep_image_launch<R, MAXT, MINB, LEAN>(set_attr_only, occ_out, grid, threads, smem, stream, src, dst, d_aux, params)
+#define LAUNCH(R, MAXT, MINB, I) sweep_image_launch<R, MAXT, MINB, I>(set_attr_only, occ_out, grid, threads, smem, stream, src, dst, d_aux, params)
+#define BY_IMG(R, MAXT, MINB) \
+    (img == IMG_FFT ? LAUNCH(R, MAXT, MINB, IMG_FFT) : img == IMG_LEAN ? LAUNCH(R, MAXT, MINB, IMG_LEAN) : LAUNCH(R, MAXT, MINB, IMG_FULL))
     const bool dbl = ctx->dtype == QSV_C128;
-    if (k > 11) {
-        if (dbl) return lean ? IMG(double, 256, 1, true) : IMG(double, 256, 1, false);
-        return lean ? IMG(float, 256, 1, true) : IMG(float, 256, 1, false);
-    }
-    if (dbl) return lean ? IMG(double, 128, 3, true) : IMG(double, 128, 3, false);
-    return lean ? IMG(float, 128, 3, true) : IMG(float, 128, 3, false);
-#undef IMG
+    if (k > 11) return dbl ? BY_IMG(double, 256, 1) : BY_IMG(float, 256, 1);
+    return dbl ? BY_IMG(double, 128, 3) : BY_IMG(float, 128, 3);
+#undef BY_IMG
+#undef LAUNCH
 }
 
 static int sweep_set_smem_attr(qsv_ctx* ctx, int k) {
     const size_t smem = 2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2);
-    for (int lean = 0; lean < 2; ++lean) {
-        cudaError_t e = sweep_image(ctx, k, lean != 0, true, nullptr, 0, 0, smem, nullptr, nullptr, nullptr, nullptr, nullptr);
+    for (int img = 0; img < 3; ++img) {
+        cudaError_t e = sweep_image(ctx, k, img, true, nullptr, 0, 0, smem, nullptr, nullptr, nullptr, nullptr, nullptr);
         if (e != cudaSuccess) return qsv_fail(ctx, QSV_E_CUDA, "cudaFuncSetAttribute(%zu B smem) failed: %s", smem, cudaGetErrorString(e));
     }
     return QSV_OK;
 }
 
 static int sweep_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const double* d_aux, const SweepParams& params,
-                        cudaStream_t stream, bool lean = false) {
+                        cudaStream_t stream, int img = IMG_FULL) {
     int sm_count = 148;
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
     const size_t smem = 2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2);
     const int threads = std::max(32, 1 << (k - RB));
     const uint64_t n_tiles = 1ull << (n - k);
     int occ = 1;
-    sweep_image(ctx, k, lean, false, &occ, 0, threads, smem, stream, nullptr, nullptr, nullptr, nullptr);
+    sweep_image(ctx, k, img, false, &occ, 0, threads, smem, stream, nullptr, nullptr, nullptr, nullptr);
     occ = std::max(occ, 1);
     const unsigned grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)sm_count * occ);
-    QSV_CUDA(ctx, sweep_image(ctx, k, lean, false, nullptr, grid, threads, smem, stream, src, dst, d_aux, &params));
+    QSV_CUDA(ctx, sweep_image(ctx, k, img, false, nullptr, grid, threads, smem, stream, src, dst, d_aux, &params));
     return QSV_OK;
 }
 
@@ -1511,7 +1893,7 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
             QSV_CUDA(ctx, cudaEventRecord(ev0, stream));
         }
         {
-            int rc = sweep_launch(ctx, n, k, cur, dstp, plan->d_aux, *st.params, stream, st.lean);
+            int rc = sweep_launch(ctx, n, k, cur, dstp, plan->d_aux, *st.params, stream, st.img);
             if (rc) return rc;
         }
         static const bool sync_each = getenv("QSV_SYNC") != nullptr;  // debugging aid: surface kernel faults at the launch site
@@ -1552,4 +1934,198 @@ int sweep_plan_collect_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out) {
     }
     if (n_out) *n_out = n;
     return QSV_OK;
+}
+
+// ================================================================================================
+// Host check of the fusion pass (TEST INFRASTRUCTURE, see include/qsv_hostcheck.h)
+// ================================================================================================
+// Interprets a fused plan on the host, thread by thread, with the SAME op functions the kernel is compiled from
+// (generic_op / fstage_op are __host__ __device__) and the same address tables (swizzled tile slots, per-slot
+// global offsets, per-tile scalars).  It exists so that the planner -- stage selection, phase polynomials,
+// relabelling, budgets, FFT-shape conversion -- can be fuzzed against the oracle on a machine without a GPU.
+// It is not a compute path: nothing in the package calls it, and it refuses states of more than 2^22 amplitudes.
+template <typename R>
+static int sweep_emulate_host(qsv_ctx* ctx, const SweepParams& P, const std::vector<double>& auxv, int img,
+                              const typename cplx_of<R>::type* src, typename cplx_of<R>::type* dst) {
+    typedef typename cplx_of<R>::type C;
+    const SweepDesc& D = P.d;
+    if (D.xg) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "hostcheck: exchange sweeps are not emulated");
+    const int k = D.k;
+    const uint32_t tile_amps = 1u << k;
+    const uint32_t threads = (uint32_t)std::max(32, 1 << (k - RB));  // as sweep_launch
+    const uint32_t n_groups = tile_amps >> RB;
+    const uint64_t n_tiles = 1ull << (D.n_bits - k);
+    const double2* aux2 = reinterpret_cast<const double2*>(auxv.data());
+    const bool dstore = D.direct_store;
+    // (inactive threads of tiny tiles read beyond the tile like the device does beyond its buffer: give them room)
+    std::vector<C> tile_v(std::max<size_t>(tile_amps, 1024));
+    C* tile = tile_v.data();
+    std::vector<double2> smE(MAX_GSLOT), smT(MAX_TAB);
+    for (uint32_t i = 0; i < D.tab_len; ++i) smT[i] = aux2[D.tab_off + i];
+    std::vector<C> regs((size_t)threads * NREG);
+    std::vector<uint32_t> base_l(threads), swbase(threads);
+    for (uint64_t t = 0; t < n_tiles; ++t) {
+        for (uint32_t gs = 0; gs < (uint32_t)D.n_gslots; ++gs) {
+            const double2* gt = aux2 + D.gtab_off + (size_t)gs * D.g_chunks * 16;
+            double2 e = gt[t & 15ull];
+            for (int c = 1; c < D.g_chunks; ++c) e = cmul(e, gt[c * 16 + ((t >> (4 * c)) & 15ull)]);
+            smE[gs] = e;
+        }
+        const uint64_t gin = seg_apply64x(t, D.in_glob), gout = seg_apply64x(t, D.out_glob);
+        auto n_slots_of = [&](uint32_t tid) { return (tid < tile_amps) ? (int)std::max(1u, tile_amps >> D.tb) : 0; };
+        for (uint32_t tid = 0; tid < threads; ++tid) {
+            const uint64_t gb = gin | seg_apply64(tid, D.in_loc);
+            for (int i = 0; i < n_slots_of(tid); ++i) tile[swz(tid) ^ D.ld_soff[i]] = src[gb | D.ld_goff[i]];
+        }
+        auto st_parts = [&](uint32_t tid, uint64_t* t_st_g, uint32_t* t_st_s) {
+            const uint32_t t_st_l = dstore ? expand_rb(tid, D.last_rpos) : seg_apply(tid, D.st_enum);
+            *t_st_g = seg_apply64(t_st_l, D.out_loc);
+            *t_st_s = swz(t_st_l);
+        };
+        bool stored = false, have_stage = false;
+        uint64_t stq[4] = {0, 0, 0, 0};
+        auto roff_of = [&](int j) { return (uint32_t)(stq[j >> 2] >> (16 * (j & 3))) & 0xFFFFu; };
+        for (int i = 0; i < D.n_ops; ++i) {
+            const OpR op = fetch_op(P.ops, i);
+            const uint32_t type = op.type();
+            if (img == IMG_FFT) {
+                if (type < DC_FSTAGE || type >= DC_FIRST_FULL) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: op %d of an FFT launch is not OP_FSTAGE", i);
+                const bool to_hbm = dstore && i == D.n_ops - 1;
+                for (uint32_t tid = 0; tid < threads; ++tid) {
+                    const bool active = tid < n_groups;
+                    uint64_t t_st_g;
+                    uint32_t t_st_s;
+                    st_parts(tid, &t_st_g, &t_st_s);
+                    const uint64_t gbs = gout | t_st_g;
+#define FS(NH, HAS_W) fstage_op<C, R, NH, HAS_W>(op, tile, smT.data(), smE.data(), tid, active, to_hbm, dst, gbs, D.st_goff); break;
+                    switch (type - DC_FSTAGE) {
+                        case 0: case 1: FS(0, false)
+                        case 2: FS(1, false)
+                        case 3: FS(1, true)
+                        case 4: FS(2, false)
+                        case 5: FS(2, true)
+                        case 6: FS(3, false)
+                        case 7: FS(3, true)
+                        case 8: FS(4, false)
+                        default: FS(4, true)
+                    }
+#undef FS
+                }
+                stored = to_hbm;
+                continue;
+            }
+            if (type >= DC_FSTAGE && type < DC_FIRST_FULL) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: OP_FSTAGE in a generic launch");
+            if (img == IMG_LEAN && type >= DC_FIRST_FULL) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: full-image op %u in a lean launch", type);
+            if (type == DC_STAGE) {
+                if (have_stage)
+                    for (uint32_t tid = 0; tid < n_groups && tid < threads; ++tid)
+                        for (int j = 0; j < NREG; ++j) tile[swbase[tid] ^ roff_of(j)] = regs[(size_t)tid * NREG + j];
+                have_stage = true;
+                stq[0] = op.p[0]; stq[1] = op.p[1]; stq[2] = op.p[2]; stq[3] = op.p[3];
+                for (uint32_t tid = 0; tid < threads; ++tid) {
+                    uint32_t b = tid;
+                    for (int q = 0; q < RB; ++q) {
+                        const uint32_t pz = op.rpos(q);
+                        b = ((b >> pz) << (pz + 1)) | (b & ((1u << pz) - 1u));
+                    }
+                    base_l[tid] = b;
+                    swbase[tid] = swz(b);
+                    if (tid < n_groups)
+                        for (int j = 0; j < NREG; ++j) regs[(size_t)tid * NREG + j] = tile[swbase[tid] ^ roff_of(j)];
+                }
+                continue;
+            }
+            if (!have_stage) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: op %d before any stage", i);
+            if (op.gmask && (t & op.gmask) != op.gval) continue;
+            for (uint32_t tid = 0; tid < n_groups && tid < threads; ++tid) {
+                const bool tpred = (base_l[tid] & op.lmask()) == op.lval();
+                C v[NREG];
+                for (int j = 0; j < NREG; ++j) v[j] = regs[(size_t)tid * NREG + j];
+                if (img == IMG_LEAN) generic_op<C, R, true>(v, op, type, tpred, smT.data(), smE.data(), tid);
+                else generic_op<C, R, false>(v, op, type, tpred, smT.data(), smE.data(), tid);
+                for (int j = 0; j < NREG; ++j) regs[(size_t)tid * NREG + j] = v[j];
+            }
+        }
+        if (stored) continue;
+        if (dstore && have_stage) {
+            for (uint32_t tid = 0; tid < n_groups && tid < threads; ++tid) {
+                uint64_t t_st_g;
+                uint32_t t_st_s;
+                st_parts(tid, &t_st_g, &t_st_s);
+                for (int j = 0; j < NREG; ++j) dst[gout | t_st_g | D.st_goff[j]] = regs[(size_t)tid * NREG + j];
+            }
+            continue;
+        }
+        if (have_stage)
+            for (uint32_t tid = 0; tid < n_groups && tid < threads; ++tid)
+                for (int j = 0; j < NREG; ++j) tile[swbase[tid] ^ roff_of(j)] = regs[(size_t)tid * NREG + j];
+        // (in place: every tile reads before it writes and tiles are disjoint, exactly as on the device)
+        for (uint32_t tid = 0; tid < threads; ++tid) {
+            uint64_t t_st_g;
+            uint32_t t_st_s;
+            st_parts(tid, &t_st_g, &t_st_s);
+            for (int i = 0; i < n_slots_of(tid); ++i) dst[gout | t_st_g | D.st_goff[i]] = tile[t_st_s ^ D.st_soff[i]];
+        }
+    }
+    return QSV_OK;
+}
+
+template <typename R>
+static int hostcheck_run(qsv_ctx* ctx, SweepPlan* plan, void* state, uint64_t* out_sweeps, uint64_t* out_fft_sweeps) {
+    typedef typename cplx_of<R>::type C;
+    const size_t amps = (size_t)1 << ctx->prog_bits;
+    std::vector<C> spare_v(amps);
+    C* cur = static_cast<C*>(state);
+    C* other = spare_v.data();
+    uint64_t sweeps = 0, fft = 0;
+    for (auto& st : plan->steps) {
+        if (!st.fused) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "hostcheck: the plan holds a gate that is not fused (dense-k / row pair)");
+        C* d = st.out_of_place ? other : cur;
+        int rc = sweep_emulate_host<R>(ctx, *st.params, plan->aux, st.img, cur, d);
+        if (rc) return rc;
+        if (st.out_of_place) std::swap(cur, other);
+        ++sweeps;
+        fft += st.img == IMG_FFT;
+    }
+    if (cur != static_cast<C*>(state)) memcpy(state, cur, amps * sizeof(C));
+    if (out_sweeps) *out_sweeps = sweeps;
+    if (out_fft_sweeps) *out_fft_sweeps = fft;
+    return QSV_OK;
+}
+
+extern "C" int qsv_hostcheck_fused(int dtype, int n_bits, const qsv_gate_t* gates, uint64_t n_gates, const double* pool, uint64_t pool_elems,
+                                   int max_tile_bits, void* state, uint64_t* out_sweeps, uint64_t* out_fft_sweeps, char* err,
+                                   uint64_t err_len) {
+    qsv_ctx ctx;  // never touches a device
+    ctx.dtype = dtype;
+    int rc = QSV_OK;
+    if ((dtype != QSV_C128 && dtype != QSV_C64) || n_bits < RB || n_bits > 22 || !state || (n_gates && !gates)) {
+        rc = qsv_fail(&ctx, QSV_E_INVALID, "hostcheck: bad arguments (n_bits must be %d..22)", RB);
+    } else {
+        for (uint64_t i = 0; i < n_gates && !rc; ++i) {
+            const qsv_gate_t& g = gates[i];
+            if (g.kind > QSV_DIAG1 || g.n_targets != 1 || g.target_bits[0] >= n_bits || (g.ctrl_mask >> n_bits) ||
+                (g.ctrl_mask & (1ull << g.target_bits[0])) || (g.ctrl_value & ~g.ctrl_mask) ||
+                (g.kind != QSV_PERMX && g.matrix_offset + 4 > pool_elems))
+                rc = qsv_fail(&ctx, QSV_E_INVALID, "hostcheck: gate %llu is not a valid one-target gate", (unsigned long long)i);
+        }
+    }
+    SweepPlan* plan = nullptr;
+    if (!rc) {
+        ctx.gates.assign(gates, gates + n_gates);
+        ctx.pool.assign(pool, pool + 2 * pool_elems);
+        ctx.prog_bits = n_bits;
+        ctx.has_program = true;
+        rc = sweep_plan_build_host(&ctx, max_tile_bits, &plan);
+    }
+    if (!rc) {
+        rc = dtype == QSV_C128 ? hostcheck_run<double>(&ctx, plan, state, out_sweeps, out_fft_sweeps)
+                               : hostcheck_run<float>(&ctx, plan, state, out_sweeps, out_fft_sweeps);
+    }
+    if (plan) sweep_plan_free(plan);
+    if (err && err_len) {
+        strncpy(err, ctx.err, err_len - 1);
+        err[err_len - 1] = 0;
+    }
+    return rc;
 }

@@ -1,0 +1,136 @@
+"""The fusion pass (host code of libqsv) checked WITHOUT a GPU: ``qsv_hostcheck_fused`` interprets the fused plan on
+the host with the same per-op source the CUDA kernel is compiled from (include/qsv_hostcheck.h), and the result must
+match the CPU oracle.  Covers what the GPU fuzz covers (tools/fuzz_fused.py) plus circuits built to hit the FFT-shaped
+launches (OP_FSTAGE) in all their shapes."""
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+
+from tests.hostcheck import ROOT, run_fused_on_host
+from oracle import sv_oracle
+from quantum_simulations_b200.construct.qspace import Qubit
+from quantum_simulations_b200.program import Program
+from quantum_simulations_b200.utils.mgen import qft_program
+
+H = np.array([[1, 1], [1, -1]]) / np.sqrt(2)
+X = np.array([[0, 1], [1, 0]], dtype=complex)
+
+
+def _fuzz_module():
+    spec = importlib.util.spec_from_file_location("fuzz_fused", os.path.join(ROOT, "tools", "fuzz_fused.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+def _state(rng, n):
+    x = rng.standard_normal(1 << n) + 1j * rng.standard_normal(1 << n)
+    return x / np.linalg.norm(x)
+
+
+def _check(prog, n, x, tile_bits, tol=1e-12, dtype=np.complex128):
+    recs, pool = prog.records(0), prog.pool()
+    got, sweeps, fft = run_fused_on_host(recs, pool, x, n, tile_bits, dtype=dtype)
+    ref = x.astype(np.complex128).copy()
+    sv_oracle.run_records(recs, pool, ref, n)
+    err = float(np.abs(got - ref).max())
+    assert err < tol, (n, tile_bits, len(prog), sweeps, fft, err)
+    return sweeps, fft
+
+
+@pytest.mark.parametrize("n,tile_bits", [(5, 0), (9, 0), (12, 0), (12, 9), (13, 11), (14, 9), (16, 11), (17, 10), (18, 12)])
+def test_qft_fused_plan_matches_oracle_and_fft(n, tile_bits):
+    rng = np.random.default_rng(100 + n)
+    x = _state(rng, n)
+    prog = qft_program(n)
+    sweeps, fft = _check(prog, n, x, tile_bits)
+    got, _, _ = run_fused_on_host(prog.records(0), prog.pool(), x, n, tile_bits)
+    assert np.abs(got - np.fft.ifft(x, norm="ortho")).max() < 1e-12
+    if n >= 13:
+        assert fft >= 1, "QFT sweeps are expected to run in the FFT-shaped image"
+
+
+def _fft_like_program(rng, n, ordered):
+    """Hadamards in random qubit order, each followed by a random subset of controlled phases (control on 1 or 0, with or
+    without a phase on the control alone) and plain phase gates.  ``ordered``: phases couple a qubit only to qubits whose
+    Hadamard comes later (the QFT discipline, in any qubit order) -- the shape OP_FSTAGE is made for, in all its variants;
+    otherwise any partner, which the fusion pass must recognise as NOT FFT-shaped where it matters."""
+    prog = Program([Qubit(i) for i in range(n)])
+    order = rng.permutation(n)
+    done = []
+    for t in order:
+        t = int(t)
+        if ordered or rng.random() < 0.85:
+            prog.add_raw([t], 0, 0, H)
+        others = [int(b) for b in range(n) if b != t and not (ordered and b in done)]
+        for c in others:
+            if rng.random() < 0.55:
+                d = np.array([1.0, np.exp(1j * rng.uniform(0, 2 * np.pi))])
+                val = 1 << c
+                if not ordered:
+                    if rng.random() < 0.1:
+                        d[0] = np.exp(1j * rng.uniform(0, 2 * np.pi))
+                    if rng.random() < 0.15:
+                        val = 0
+                prog.add_raw([t], 1 << c, val, np.diag(d))
+        if rng.random() < 0.3:
+            prog.add_raw([t], 0, 0, np.diag(np.exp(1j * rng.uniform(0, 2 * np.pi, 2))))
+        done.append(t)
+    return prog
+
+
+@pytest.mark.parametrize("ordered", [True, False])
+@pytest.mark.parametrize("seed", range(12))
+def test_fft_shaped_circuits(seed, ordered):
+    rng = np.random.default_rng(seed)
+    n = int(rng.integers(9, 17))
+    prog = _fft_like_program(rng, n, ordered)
+    x = _state(rng, n)
+    total_fft = 0
+    for tb in (0, 9, 11):
+        if tb > n:
+            continue
+        _, fft = _check(prog, n, x, tb)
+        total_fft += fft
+    if ordered:
+        assert total_fft >= 1, "circuits with the QFT discipline are expected to run in the FFT-shaped image"
+
+
+def test_hadamard_layers_and_scale():
+    """Pure Hadamard layers: butterflies without tables; the owed 1/sqrt2^k scale is settled once per sweep."""
+    rng = np.random.default_rng(5)
+    for n in (10, 13, 15):
+        prog = Program([Qubit(i) for i in range(n)])
+        for t in rng.permutation(n):
+            prog.add_raw([int(t)], 0, 0, H)
+        x = _state(rng, n)
+        _, fft = _check(prog, n, x, 11 if n > 11 else 0)
+        assert fft >= 1
+
+
+@pytest.mark.parametrize("seed,tile_bits", [(1, 0), (2, 9), (3, 10), (4, 12), (5, 0), (6, 9)])
+def test_random_circuits_every_op_kind(seed, tile_bits):
+    fz = _fuzz_module()
+    rng = np.random.default_rng(seed)
+    for _ in range(10):
+        n = int(rng.integers(4, 15))
+        n_gates = int(rng.choice([5, 60, 200, 800])) if n <= 11 else int(rng.choice([20, 200]))
+        prog = fz.random_program(rng, n, n_gates)
+        _check(prog, n, _state(rng, n), tile_bits, tol=1e-11)
+
+
+def test_complex64_fused_plan():
+    rng = np.random.default_rng(9)
+    for n in (12, 14):
+        x = _state(rng, n)
+        _check(qft_program(n), n, x, 11, tol=2e-6, dtype=np.complex64)
+
+
+def test_hostcheck_rejects_bad_input():
+    prog = qft_program(5)
+    recs = prog.records(0).copy()
+    recs["target_bits"][0][0] = 9
+    with pytest.raises(RuntimeError):
+        run_fused_on_host(recs, prog.pool(), np.ones(32, dtype=complex), 5)

@@ -422,3 +422,58 @@ def test_allprop_on_device():
     a3 = (2.5 - 1j) * b3
     ok, ratio = eng.allprop(a3, b3)
     assert ok and abs(ratio - (2.5 - 1j)) < 1e-12
+
+
+@pytest.mark.parametrize("tile_bits", [0, 9, 12])
+def test_fuzz_fused_vs_per_gate_and_oracle(tile_bits, monkeypatch):
+    """Random circuits over every op kind the fusion pass knows (tools/fuzz_fused.py): the fused tile sweep, the
+    one-kernel-per-gate path and -- for the small registers -- the CPU oracle must agree to 1e-10."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location(
+        "fuzz_fused", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "fuzz_fused.py"))
+    fz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fz)
+    from oracle import sv_oracle
+    if tile_bits:
+        monkeypatch.setenv("QSV_TILE_BITS", str(tile_bits))
+    rng = np.random.default_rng(1000 + tile_bits)
+    for case in range(24):
+        n = int(rng.integers(4, 15))
+        batch = int(rng.choice([1, 2, 8]))
+        n_gates = int(rng.choice([5, 60, 200, 800])) if n <= 11 else int(rng.choice([20, 200]))
+        prog = fz.random_program(rng, n, n_gates)
+        x = rng.standard_normal((1 << n, batch)) + 1j * rng.standard_normal((1 << n, batch))
+        x /= np.linalg.norm(x, axis=0)
+        a = apply_circuit(prog, x, fuse=True)
+        b = apply_circuit(prog, x, fuse=False)
+        assert np.abs(a - b).max() < 1e-10, (case, n, batch, len(prog))
+        if n <= 10 and len(prog) <= 250:
+            bb = batch.bit_length() - 1
+            flat = x.astype(np.complex128).reshape(-1).copy()
+            sv_oracle.run_records(prog.records(bb), prog.pool(), flat, n + bb)
+            assert np.abs(a - flat.reshape(1 << n, batch)).max() < 1e-10, (case, n, batch, len(prog))
+
+
+@pytest.mark.parametrize("ordered", [True, False])
+@pytest.mark.parametrize("tile_bits", [0, 9, 11])
+def test_fft_shaped_launches_on_gpu(tile_bits, ordered, monkeypatch):
+    """Hadamard + controlled-phase circuits in random qubit order (tests/test_fusion_hostcheck.py): with the QFT
+    discipline they run in the FFT-shaped kernel image (OP_FSTAGE), without it in the generic one; both must match
+    the oracle, and the device result must match the host interpretation of the same plan to rounding."""
+    from tests.hostcheck import run_fused_on_host
+    from tests.test_fusion_hostcheck import _fft_like_program
+    if tile_bits:
+        monkeypatch.setenv("QSV_TILE_BITS", str(tile_bits))
+    rng = np.random.default_rng(77 + tile_bits)
+    for case in range(8):
+        n = int(rng.integers(9, 17))
+        prog = _fft_like_program(rng, n, ordered)
+        x = rng.standard_normal((1 << n, 1)) + 1j * rng.standard_normal((1 << n, 1))
+        x /= np.linalg.norm(x)
+        got = apply_circuit(prog, x, fuse=True)[:, 0]
+        ref = x[:, 0].copy()
+        orc.run_records(prog.records(0), prog.pool(), ref, n)
+        assert np.abs(got - ref).max() < TOL128, (case, n, len(prog))
+        host, _, _ = run_fused_on_host(prog.records(0), prog.pool(), x[:, 0], n, tile_bits if tile_bits <= n else 0)
+        assert np.abs(got - host).max() < 1e-13, (case, n, len(prog))

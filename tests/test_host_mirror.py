@@ -182,6 +182,12 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in qsv.h but not exported"
     assert declared == set(_lib.exported_symbols()), "ctypes binding and header out of sync"
+    # the test-only host check of the fusion pass has its own header and is bound under tests/, not in the package
+    hc = open(os.path.join(ROOT, "include", "qsv_hostcheck.h")).read()
+    hc_declared = set(re.findall(r"\b(qsv_[a-z0-9_]+)\s*\(", hc))
+    assert hc_declared == {"qsv_hostcheck_fused"}
+    assert hasattr(lib, "qsv_hostcheck_fused")
+    assert "qsv_hostcheck_fused" not in _lib.exported_symbols()
     assert b"sm_100a" in ctypes.cast(lib.qsv_version, ctypes.CFUNCTYPE(ctypes.c_char_p))()
 
 
