@@ -37,7 +37,10 @@
 #define NREG 16
 #define MAX_OPS 320      // ops per launch (kernel parameter space, 32 KB limit)
 #define MAX_GSLOT 96     // per-tile phase scalars per launch
-#define MAX_TAB 512      // double2 entries of phase tables per launch (8 KB of shared memory)
+#define MAX_TAB 384      // double2 entries of phase tables per launch (6 KB of shared memory)
+#define PARK_WORDS 3     // 64-bit per-thread tile-copy constants parked in shared memory (registers are at the 3-CTA/SM cap)
+#define SWEEP_SMEM(amp_bytes, k, threads) \
+    (2 * ((size_t)(amp_bytes) << (k)) + (MAX_GSLOT + MAX_TAB) * sizeof(double2) + (size_t)PARK_WORDS * (threads) * sizeof(uint64_t))
 #define TSLOT_LEN 32     // one thread-phase slot = 2 chunks x 16 entries
 #define MAX_SEG 12
 
@@ -452,8 +455,17 @@ __host__ __device__ __forceinline__ bool fstage_op(const OpR& op, C* __restrict_
         return true;
     }
     if (active) {
+        // the 16 slot numbers are rebuilt from slot 0 (15 XORs) rather than kept in registers across the arithmetic:
+        // the opaque copy stops the compiler from re-using the ones computed for the load
+        uint32_t b[NREG];
+        b[0] = a[0];
+#ifdef __CUDA_ARCH__
+        asm volatile("" : "+r"(b[0]));
+#endif
 #pragma unroll
-        for (int j = 0; j < NREG; ++j) tile[a[j]] = w[j];
+        for (int j = 1; j < NREG; ++j) b[j] = b[j & (j - 1)] ^ op.u16_at(46 + 2 * ((j & 1) ? 0 : (j & 2) ? 1 : (j & 4) ? 2 : 3));
+#pragma unroll
+        for (int j = 0; j < NREG; ++j) tile[b[j]] = w[j];
     }
 #ifdef __CUDA_ARCH__
     __syncthreads();
@@ -517,6 +529,13 @@ _Pragma("unroll") for (int j = 0; j < NREG; ++j) if ((wm >> j) & 1) {  \
 #undef DENSE_CASES
 }
 
+// gridDim.x re-read at every use: held in a register across a tile it was spilled to local memory
+__device__ __forceinline__ uint32_t grid_x() {
+    uint32_t gx;
+    asm volatile("mov.u32 %0, %%nctaid.x;" : "=r"(gx));
+    return gx;
+}
+
 template <int BYTES>
 __device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
@@ -551,22 +570,33 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
     auto buf_ptr = [&](int b) { return reinterpret_cast<C*>(smem_raw + (size_t)b * tile_bytes); };
     double2* smE = reinterpret_cast<double2*>(smem_raw + 2 * tile_bytes);
     double2* smT = smE + MAX_GSLOT;
+    uint64_t* park = reinterpret_cast<uint64_t*>(smT + MAX_TAB);  // [PARK_WORDS][blockDim]
     const double2* aux2 = reinterpret_cast<const double2*>(aux);
 
     const uint32_t tid = threadIdx.x;
     const uint32_t tile_amps = 1u << D.k;
     const uint32_t n_groups = tile_amps >> RB;
     const bool active = tid < n_groups;
-    const uint64_t n_tiles = 1ull << (D.n_bits - D.k);
+    const uint32_t n_tiles = 1u << (D.n_bits - D.k);  // (at most 2^31: checked by sweep_launch)
     // per-thread parts of the tile-copy addresses (tile independent)
     const bool dstore = D.direct_store;
-    const uint64_t t_ld_g = seg_apply64(tid, D.in_loc);
-    const uint32_t t_ld_s = swz(tid);
+    // (the two 64-bit ones live in shared memory and are re-read where needed -- one LDS each per tile: kept in
+    // registers they were spilled to local memory, whose reloads were the kernel's largest single stall)
     const uint32_t t_st_l = dstore ? expand_rb(tid, D.last_rpos) : seg_apply(tid, D.st_enum);
-    const uint64_t t_st_g = seg_apply64(t_st_l, D.out_loc);
-    const uint32_t t_st_s = swz(t_st_l);
+    volatile uint64_t* park_ld = park + tid;
+    volatile uint64_t* park_st = park + blockDim.x + tid;
+    volatile uint32_t* park_w = reinterpret_cast<volatile uint32_t*>(park + 2 * blockDim.x + tid);  // [0] store slot, [1] tile id
+    *park_ld = seg_apply64(tid, D.in_loc);
+    *park_st = seg_apply64(t_st_l, D.out_loc);
+    park_w[0] = swz(t_st_l);
+#define t_ld_g (*park_ld)
+#define t_st_g (*park_st)
+#define t_st_s (park_w[0])
     // amplitudes each thread copies (<= NREG); tiles smaller than a warp use only the first tile_amps threads
-    const int n_slots = (tid < tile_amps) ? (int)max(1u, tile_amps >> D.tb) : 0;
+    // (kept as a CTA-uniform count and a per-thread predicate rather than one per-thread integer: registers are scarce)
+    const int n_slots_u = (int)max(1u, tile_amps >> D.tb);
+    const bool copies = tid < tile_amps;
+#define n_slots (copies ? n_slots_u : 0)
 
     // phase tables of this sweep: global -> shared, once per CTA
     for (uint32_t i = tid; i < D.tab_len; i += blockDim.x) smT[i] = aux2[D.tab_off + i];
@@ -574,6 +604,7 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
     // tile prefetch: 128-bit cp.async straight into the swizzled tile buffer (no registers involved)
     auto prefetch = [&](uint64_t t, C* buf) {
         const uint64_t gb = seg_apply64x(t, D.in_glob) | t_ld_g;
+        const uint32_t t_ld_s = swz(tid);
 #pragma unroll
         for (int i = 0; i < NREG; ++i)
             if (i < n_slots) cp_async<sizeof(C)>(&buf[t_ld_s ^ D.ld_soff[i]], &src[gb | D.ld_goff[i]]);
@@ -583,7 +614,7 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
     if (blockIdx.x < n_tiles) prefetch(blockIdx.x, buf_ptr(0));
     cp_async_commit();
 
-    for (uint64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+    for (uint32_t t = blockIdx.x; t < n_tiles; t += grid_x()) {
         C* tile = buf_ptr(cur);
         // ---- per-tile phase scalars: product of 16-entry chunk tables over the tile id ---------
         for (uint32_t gs = tid; gs < (uint32_t)D.n_gslots; gs += blockDim.x) {
@@ -595,8 +626,8 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
         cp_async_wait_all();
         __syncthreads();  // tile t has landed; per-tile scalars visible; previous tile fully retired
         {
-            const uint64_t tn = t + gridDim.x;
-            if (tn < n_tiles) prefetch(tn, buf_ptr(cur ^ 1));
+            const uint32_t tn = t + grid_x();
+            if (tn > t && tn < n_tiles) prefetch(tn, buf_ptr(cur ^ 1));
             cp_async_commit();
         }
 
@@ -707,6 +738,10 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
     }
     cp_async_wait_all();
 }
+#undef t_ld_g
+#undef t_st_g
+#undef t_st_s
+#undef n_slots
 
 // ================================================================================================
 // host: fusion pass
@@ -1801,7 +1836,7 @@ static cudaError_t sweep_image(qsv_ctx* ctx, int k, int img, bool set_attr_only,
 }
 
 static int sweep_set_smem_attr(qsv_ctx* ctx, int k) {
-    const size_t smem = 2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2);
+    const size_t smem = SWEEP_SMEM(amp_size(ctx->dtype), k, std::max(32, 1 << (k - RB)));
     for (int img = 0; img < 3; ++img) {
         cudaError_t e = sweep_image(ctx, k, img, true, nullptr, 0, 0, smem, nullptr, nullptr, nullptr, nullptr, nullptr);
         if (e != cudaSuccess) return qsv_fail(ctx, QSV_E_CUDA, "cudaFuncSetAttribute(%zu B smem) failed: %s", smem, cudaGetErrorString(e));
@@ -1813,8 +1848,9 @@ static int sweep_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, 
                         cudaStream_t stream, int img = IMG_FULL) {
     int sm_count = 148;
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
-    const size_t smem = 2 * (amp_size(ctx->dtype) << k) + (MAX_GSLOT + MAX_TAB) * sizeof(double2);
     const int threads = std::max(32, 1 << (k - RB));
+    const size_t smem = SWEEP_SMEM(amp_size(ctx->dtype), k, threads);
+    if (n - k > 31) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "unsupported: %d tile-id bits (max 31)", n - k);
     const uint64_t n_tiles = 1ull << (n - k);
     int occ = 1;
     sweep_image(ctx, k, img, false, &occ, 0, threads, smem, stream, nullptr, nullptr, nullptr, nullptr);
