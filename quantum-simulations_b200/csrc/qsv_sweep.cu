@@ -36,11 +36,11 @@
 #define RB 4             // register bits per stage
 #define NREG 16
 #define MAX_OPS 320      // ops per launch (kernel parameter space, 32 KB limit)
-#define MAX_GSLOT 96     // per-tile phase scalars per launch
+#define MAX_GSLOT 48     // per-tile phase scalars per launch (double-buffered in shared memory by tile parity)
 #define MAX_TAB 384      // double2 entries of phase tables per launch (6 KB of shared memory)
 #define PARK_WORDS 3     // 64-bit per-thread tile-copy constants parked in shared memory (registers are at the 3-CTA/SM cap)
 #define SWEEP_SMEM(amp_bytes, k, threads) \
-    (2 * ((size_t)(amp_bytes) << (k)) + (MAX_GSLOT + MAX_TAB) * sizeof(double2) + (size_t)PARK_WORDS * (threads) * sizeof(uint64_t))
+    (2 * ((size_t)(amp_bytes) << (k)) + (2 * MAX_GSLOT + MAX_TAB) * sizeof(double2) + (size_t)PARK_WORDS * (threads) * sizeof(uint64_t))
 #define TSLOT_LEN 32     // one thread-phase slot = 2 chunks x 16 entries
 #define MAX_SEG 12
 
@@ -568,8 +568,8 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
     const SweepDesc& D = P.d;
     const size_t tile_bytes = (size_t)sizeof(C) << D.k;
     auto buf_ptr = [&](int b) { return reinterpret_cast<C*>(smem_raw + (size_t)b * tile_bytes); };
-    double2* smE = reinterpret_cast<double2*>(smem_raw + 2 * tile_bytes);
-    double2* smT = smE + MAX_GSLOT;
+    double2* smE0 = reinterpret_cast<double2*>(smem_raw + 2 * tile_bytes);  // [2][MAX_GSLOT]: per-tile scalars, by tile parity
+    double2* smT = smE0 + 2 * MAX_GSLOT;
     uint64_t* park = reinterpret_cast<uint64_t*>(smT + MAX_TAB);  // [PARK_WORDS][blockDim]
     const double2* aux2 = reinterpret_cast<const double2*>(aux);
 
@@ -616,6 +616,7 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
 
     for (uint32_t t = blockIdx.x; t < n_tiles; t += grid_x()) {
         C* tile = buf_ptr(cur);
+        double2* smE = smE0 + cur * MAX_GSLOT;
         // ---- per-tile phase scalars: product of 16-entry chunk tables over the tile id ---------
         for (uint32_t gs = tid; gs < (uint32_t)D.n_gslots; gs += blockDim.x) {
             const double2* gt = aux2 + D.gtab_off + (size_t)gs * D.g_chunks * 16;
@@ -733,7 +734,8 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
                 }
         }
         }  // generic images
-        __syncthreads();  // this buffer and the per-tile scalars are rewritten two / one tiles from now
+        // No barrier here: the tile buffer and the scalars of this parity are next written two tiles from now, i.e. after
+        // every thread has passed the barrier at the start of the next tile -- and so has finished this one.
         cur ^= 1;
     }
     cp_async_wait_all();
@@ -879,7 +881,10 @@ struct Builder {
 
     uint64_t forced_mask() const { return (1ull << c_low) - 1ull; }
 
-    bool fits(uint64_t targets) const { return __builtin_popcountll(targets | forced_mask()) <= k; }
+    int target_cap = 64;  // max butterfly targets per sweep (see sweep_plan_build_host: balanced sweeps)
+    bool fits(uint64_t targets) const {
+        return __builtin_popcountll(targets | forced_mask()) <= k && __builtin_popcountll(targets) <= target_cap;
+    }
 
     int add_gate(size_t gi) {
         next_gate = gi;
@@ -1755,26 +1760,55 @@ static int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** ou
         sweep_plan_free(ctx->plan);
         ctx->plan = nullptr;
     }
-    SweepPlan* plan = new SweepPlan();
-    plan->k = k;
-    plan->aux.resize(2, 0.0);  // offset 0 reserved
-    Builder b(ctx, plan, n, k);
-    for (size_t i = 0; i < ctx->gates.size(); ++i) {
-        int rc = b.add_gate(i);
+    auto build = [&](int cap, SweepPlan** out) -> int {
+        SweepPlan* plan = new SweepPlan();
+        plan->k = k;
+        plan->aux.resize(2, 0.0);  // offset 0 reserved
+        Builder b(ctx, plan, n, k);
+        b.target_cap = cap;
+        int rc = QSV_OK;
+        for (size_t i = 0; i < ctx->gates.size() && !rc; ++i) rc = b.add_gate(i);
+        if (!rc) {
+            b.next_gate = ctx->gates.size();
+            rc = b.flush();
+        }
+        if (!rc) rc = b.restore_layout();
         if (rc) {
             delete plan;
             return rc;
         }
+        plan->dropped_identities += b.relabelled_gates;  // counted as applied source gates
+        *out = plan;
+        return QSV_OK;
+    };
+    SweepPlan* best = nullptr;
+    {
+        int rc = build(64, &best);
+        if (rc) return rc;
     }
-    b.next_gate = ctx->gates.size();
-    int rc = b.flush();
-    if (!rc) rc = b.restore_layout();
-    if (rc) {
-        delete plan;
-        return rc;
+    // Balanced sweeps: a sweep's cost grows with the butterflies it carries, so among the plans with the FEWEST launches
+    // take the one with the smallest per-sweep target count (QFT-30 at k = 11: 6+6+6+6+6 instead of 7+7+7+7+2; measured
+    // 33.6 vs 34.1 ms).  Planning is host work of O(gates); the search is skipped for very long programs.
+    static const char* cap_env = getenv("QSV_SWEEP_TARGETS");  // tuning aid: fixed cap, no search
+    if (cap_env) {
+        SweepPlan* p = nullptr;
+        if (build(atoi(cap_env), &p) == QSV_OK) {
+            delete best;
+            best = p;
+        }
+    } else if (ctx->gates.size() <= 50000 && k < n) {
+        for (int cap = k - 2; cap >= 3; --cap) {
+            SweepPlan* p = nullptr;
+            if (build(cap, &p) != QSV_OK) break;
+            if (p->steps.size() > best->steps.size()) {
+                delete p;
+                break;
+            }
+            delete best;
+            best = p;
+        }
     }
-    plan->dropped_identities += b.relabelled_gates;  // counted as applied source gates
-    *out_plan = plan;
+    *out_plan = best;
     return QSV_OK;
 }
 
