@@ -185,3 +185,63 @@ def test_two_process_gloo_half_state_swap(tmp_path):
     x = random_state(1 << n)
     got = np.concatenate([np.load(tmp_path / f"shard{r}.npy") for r in range(world)])
     assert np.abs(got - orc.qft_reference(x)).max() < 1e-12
+
+
+class FusedHostExecutor(OracleExecutor):
+    """Local executor that runs every segment through the REAL fusion pass, interpreted on the host
+    (tests/hostcheck.py): the per-rank records of ``localize_records`` go through the same planner -- tile choice,
+    phase polynomials, SWAP relabels, FFT-shaped launches -- that the GPU executor feeds to k_sweep."""
+
+    def __init__(self):
+        super().__init__()
+        self.fft_sweeps = 0
+
+    def run_segment(self, key, state, spare):
+        from tests.hostcheck import run_fused_on_host
+        recs, pool, n_loc = self.segs[key]
+        if len(recs) == 0:
+            return state, spare
+        out, _, fft = run_fused_on_host(recs, pool, state, n_loc)
+        self.fft_sweeps += fft
+        state[:] = out
+        return state, spare
+
+
+@pytest.mark.parametrize("world,n", [(2, 13), (4, 14), (8, 15), (8, 16)])
+def test_qft_sharded_through_the_fusion_pass(world, n):
+    """Sharding planner + rank localisation + fusion pass end to end on CPU: every rank's segments are planned and
+    interpreted by libqsv's host check, exchanges are emulated in memory, the result is the FFT of the input."""
+    prog = qft_program(n)
+    recs, pool = prog.records(), prog.pool()
+    x = random_state(1 << n)
+    g = world.bit_length() - 1
+    n_loc = n - g
+    shards = [x[r << n_loc:(r + 1) << n_loc].copy() for r in range(world)]
+    spares = [np.zeros_like(s) for s in shards]
+    fw = FakeWorld(shards)
+
+    class NullEx:
+        def exchange(self, state, spare, gbit):
+            return state
+
+        def exchange_all(self, state, spare):
+            return state, spare
+
+    circs = [ShardedCircuit(recs, pool, n, r, world, FusedHostExecutor(), NullEx()) for r in range(world)]
+    plan = circs[0].plan
+    li = 0
+    for s in plan.steps:
+        if s[0] == "local":
+            for r in range(world):
+                fw.shards[r], spares[r] = circs[r].executor.run_segment(li, fw.shards[r], spares[r])
+            li += 1
+        elif s[0] == "exchange":
+            fw.exchange_pair(s[1])
+        elif s[0] == "xall":
+            fw.exchange_all()
+        else:
+            for r in range(world):
+                fw.shards[r], spares[r] = circs[r].executor.permute(fw.shards[r], spares[r], n_loc, s[1])
+    got = np.concatenate(fw.shards)
+    assert np.abs(got - np.fft.ifft(x, norm="ortho")).max() < 1e-12
+    assert sum(c.executor.fft_sweeps for c in circs) >= world, "local QFT segments are expected to be FFT-shaped launches"
