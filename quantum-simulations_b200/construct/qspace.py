@@ -10,17 +10,22 @@ from functools import total_ordering
 
 @total_ordering
 class Qubit:
-    __slots__ = ("qid", "ancilla")
+    __slots__ = ("qid", "ancilla", "_h")
 
     def __init__(self, qid: int, ancilla: bool = False):
         assert qid >= 0, f'Qubit {qid} must be >= 0'
         self.qid = int(qid)
         self.ancilla = bool(ancilla)
+        # same value as the reference (qspace.py:27-28) so mixed dict lookups agree; cached: gate streams hash
+        # their qubits millions of times
+        self._h = hash(self.qid) + hash(self.ancilla)
 
     def _key(self):
         return (self.ancilla, self.qid)
 
     def __eq__(self, other):
+        if other.__class__ is Qubit:
+            return self.qid == other.qid and self.ancilla == other.ancilla
         if not _is_qubit(other):
             return NotImplemented
         return self._key() == (bool(other.ancilla), int(other.qid))
@@ -31,8 +36,7 @@ class Qubit:
         return self._key() < (bool(other.ancilla), int(other.qid))
 
     def __hash__(self):
-        # same value as the reference (qspace.py:27-28) so mixed dict lookups agree
-        return hash(self.qid) + hash(self.ancilla)
+        return self._h
 
     def __repr__(self):
         return f"{'a' if self.ancilla else 'q'}{self.qid}"
@@ -51,6 +55,7 @@ class Qubit:
             state = state[1] or state[0]
         self.qid = int(state["qid"])
         self.ancilla = bool(state["ancilla"])
+        self._h = hash(self.qid) + hash(self.ancilla)
 
 
 def _is_qubit(x) -> bool:
