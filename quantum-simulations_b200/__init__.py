@@ -8,10 +8,11 @@ from .construct.su2gate import RGate
 from .construct.types import GateGrain, PrincipalAxis, QompilePlatform, QType, UnivGate
 from .construct.unitary import UnitaryM
 from .circuits.b200_builder import B200Builder, B200Circuit
+from .circuits.qasm_builder import QasmBuilder, QasmCircuit, parse_qasm
 from .circuits.qbuilder import CircuitBuilder
 from .circuits.qfactory import get_builder, get_render
 from .circuits.render import QRenderer
 
 __all__ = ["Bytecode", "BytecodeIter", "BytecodeRevIter", "CtrlGate", "GateChain", "Qubit", "RGate", "GateGrain",
            "PrincipalAxis", "QompilePlatform", "QType", "UnivGate", "UnitaryM", "B200Builder", "B200Circuit",
-           "CircuitBuilder", "get_builder", "get_render", "QRenderer"]
+           "CircuitBuilder", "get_builder", "get_render", "QRenderer", "QasmBuilder", "QasmCircuit", "parse_qasm"]

@@ -6,13 +6,16 @@ for them raises the same ``ValueError`` the reference raises for an unknown plat
 """
 from ..construct.types import QompilePlatform
 from .b200_builder import B200Builder
+from .qasm_builder import QasmBuilder
 from .render import QRenderer
 
 
-def get_builder(target) -> B200Builder:
+def get_builder(target):
     name = getattr(target, "name", str(target))
     if name == QompilePlatform.B200.name:
         return B200Builder()
+    if name == QompilePlatform.QASM.name:
+        return QasmBuilder()
     raise ValueError(f"Unsupported platform {target}")
 
 

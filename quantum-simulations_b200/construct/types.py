@@ -162,6 +162,7 @@ class QompilePlatform(Enum):
     QISKIT = 'QiskitBuilder'
     QUIMB = 'QuimbBuilder'
     B200 = 'B200Builder'  # new target: the CUDA statevector engine of this repo
+    QASM = 'QasmBuilder'  # new target: OpenQASM 3 text (what the demos get from qiskit's qasm.dumps)
 
     def __repr__(self):
         return self.name

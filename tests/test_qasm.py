@@ -1,0 +1,156 @@
+"""OpenQASM 3 exporter (circuits/qasm_builder.py): the text parses back into the gate program it was
+built from, and that program reproduces the circuit's unitary on the oracle (CPU) and on the CUDA engine (GPU).
+Parity with qiskit's ``qasm.dumps`` is UNPINNED (qiskit is not installed)."""
+import cmath
+import random
+import warnings
+
+import numpy as np
+import pytest
+
+import quantum_simulations_b200 as qs
+from oracle import sv_oracle as orc
+from quantum_simulations_b200.circuits.qasm_builder import QasmBuilder, parse_qasm, u_matrix, zyz_angles
+from quantum_simulations_b200.utils.mgen import random_ctrlgate, random_unitary
+from tests.golden_io import load, unpack_gates
+
+T, C0, C1 = qs.QType.TARGET, qs.QType.CONTROL0, qs.QType.CONTROL1
+
+
+def _unitary_of(prog):
+    """Dense operator of a Program over all its qubits, by the oracle (columns = basis states)."""
+    n = prog.n_qubits
+    st = np.eye(1 << n, dtype=np.complex128).reshape(-1).copy()
+    orc.run_records(prog.records(n), prog.pool(), st, 2 * n)
+    return st.reshape(1 << n, 1 << n)
+
+
+def test_zyz_angles_cover_the_degenerate_cases():
+    np.random.seed(4)
+    mats = [random_unitary(2) for _ in range(50)]
+    mats += [np.diag(np.exp(1j * np.random.uniform(0, 6, 2))) for _ in range(10)]
+    mats += [np.array([[0, 1], [1, 0]]) @ np.diag(np.exp(1j * np.random.uniform(0, 6, 2))) for _ in range(10)]
+    mats += [np.array(g) for g in qs.UnivGate]
+    for m in mats:
+        t, p, l, g = zyz_angles(m)
+        assert np.abs(cmath.exp(1j * g) * u_matrix(t, p, l) - m).max() < 1e-13
+
+
+def _random_one_target_gates(n, count, seed):
+    random.seed(seed)
+    np.random.seed(seed)
+    gates = []
+    for _ in range(count):
+        k = random.randint(1, min(4, n))
+        g = random_ctrlgate(k, 1, qnum=n)
+        r = random.random()
+        ph = np.exp(1j * np.random.uniform(0, 6.28)) if random.random() < 0.5 else 1.0
+        if r < 0.3:
+            g = qs.CtrlGate(random.choice(list(qs.UnivGate)), g.controls(), g.qspace, phase=ph)
+        elif r < 0.5:
+            g = qs.CtrlGate(qs.RGate(np.random.uniform(-3, 3), random.choice(list(qs.PrincipalAxis))), g.controls(), g.qspace, phase=ph)
+        elif r < 0.6:
+            g = qs.CtrlGate(np.diag(np.exp(1j * np.random.uniform(0, 6.28, 2))), g.controls(), g.qspace)
+        gates.append(g)
+    return gates
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_text_round_trips_to_the_same_operator(seed):
+    n = 5
+    gates = _random_one_target_gates(n, 60, seed)
+    reg = [qs.Qubit(i) for i in range(n)]
+    b = QasmBuilder()
+    b.register(reg)
+    for g in gates:
+        b.build_gate(g)
+    circ = b.finish()
+    text = circ.qasm()
+    assert text.startswith("OPENQASM 3.0;") and f"qubit[{n}] q;" in text and len(circ) == len(gates)
+    got = _unitary_of(parse_qasm(text))
+    want = orc.simulate(gates, reg, np.eye(1 << n, dtype=np.complex128))
+    assert np.abs(got - want).max() < 1e-12
+    # names: standard gates and principal rotations are written by name, the rest as U(...)
+    assert any(re_ in text for re_ in ("rx(", "ry(", "rz(")) and "U(" in text and "negctrl @" in text and "gphase(" in text
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg2s", "cfg2c", "r4singlet", "r4principal", "r4univ_gate"])
+def test_compiled_streams_export_and_reproduce_their_unitary(name):
+    """The reference's compiled gate streams (golden fixtures): exported, parsed back, simulated with ancillas in |0>
+    and projected on <0| -- equals the unitary that was compiled."""
+    d = load("streams")
+    leaves = unpack_gates(d, name)                  # matrix-product order
+    b = QasmBuilder()
+    for g in leaves[::-1]:                           # circuit time order, as QRenderer feeds a builder
+        b.build_gate(g)
+    circ = b.finish()
+    prog = circ.program()
+    n, am = prog.n_qubits, prog.ancilla_mask
+    keep = [i for i in range(1 << n) if not (i & am)]
+    k = len(keep).bit_length() - 1
+    st = np.zeros((1 << n, 1 << k), dtype=np.complex128)
+    st[keep, np.arange(len(keep))] = 1
+    flat = st.reshape(-1)
+    orc.run_records(prog.records(k), prog.pool(), flat, n + k)
+    got = flat.reshape(1 << n, 1 << k)[keep, :]
+    assert np.abs(got - d[f"{name}_value"]).max() < 1e-10
+    if am:
+        assert "] a;" in circ.qasm()
+
+
+def test_builder_protocol():
+    b = qs.get_builder(qs.QompilePlatform.QASM)
+    assert isinstance(b, QasmBuilder)
+    b.register([qs.Qubit(1), qs.Qubit(0)])
+    b.register([qs.Qubit(1), qs.Qubit(7, True)])            # overlapping registrations are fine
+    assert [repr(q) for q in b.all_qubits()] == ["q0", "q1", "a7"]
+    b.build_gate(qs.CtrlGate(qs.UnivGate.H, [T], [qs.Qubit(1)]))
+    first = b.finish().qasm()
+    b.build_gate(qs.CtrlGate(qs.UnivGate.X, [C1, T], [qs.Qubit(7, True), qs.Qubit(0)]))
+    second = b.finish()                                      # finish may be called more than once
+    assert first.count("\n") + 1 == second.qasm().count("\n") and "ctrl @ x a[0], q[0];" in second.qasm()
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        b.build_gate(qs.UnitaryM(4, (1, 2), random_unitary(2)))
+    assert w and "ignored" in str(w[0].message)
+    with pytest.raises(NotImplementedError):
+        b.build_gate(random_ctrlgate(3, 2, qnum=3))
+        b.finish()
+    with pytest.raises(ValueError):
+        parse_qasm("OPENQASM 3.0;\nqubit[1] q;\nfoo q[0];\n")
+    with pytest.raises(ValueError):
+        parse_qasm(second.qasm(), qubits=[qs.Qubit(0)])
+
+
+def test_qubit_order_permutes_the_operator():
+    gates = _random_one_target_gates(3, 10, 8)
+    reg = [qs.Qubit(i) for i in range(3)]
+    b = QasmBuilder()
+    b.register(reg)
+    for g in gates:
+        b.build_gate(g)
+    circ = b.finish()
+    order = [reg[2], reg[0], reg[1]]
+    got = _unitary_of(circ.program(order))
+    want = orc.simulate(gates, order, np.eye(8, dtype=np.complex128))
+    assert np.abs(got - want).max() < 1e-12
+
+
+@pytest.mark.gpu
+def test_text_evaluated_by_the_cuda_engine():
+    d = load("streams")
+    for name in ("cfg1", "cfg2s"):
+        b = QasmBuilder()
+        for g in unpack_gates(d, name)[::-1]:
+            b.build_gate(g)
+        got = b.finish().unitary(drop_ancilla=True)
+        assert np.abs(got - d[f"{name}_value"]).max() < 1e-10
+    gates = _random_one_target_gates(4, 40, 5)
+    reg = [qs.Qubit(i) for i in range(4)]
+    b = QasmBuilder()
+    b.register(reg)
+    for g in gates:
+        b.build_gate(g)
+    got = b.finish().unitary()
+    want = orc.simulate(gates, reg, np.eye(16, dtype=np.complex128))
+    assert np.abs(got - want).max() < 1e-10
