@@ -319,8 +319,56 @@ def gen_qco():
     np.savez_compressed(os.path.join(OUT, "qco_inputs.npz"), **out)
 
 
+def gen_optimizer():
+    """SlidingWindowCombiner (optimize/basic_optimizer.py:11-49, window.py:25-104) run by the real reference on flat
+    leaf lists: the un-optimised compiled leaves of several unitaries / emit levels / window sizes, plus hand-made
+    sequences (HXH, TT, SS, XX, identities, interleaved qubits).  Stored: leaves before, leaves after."""
+    from quompiler.construct.bytecode import Bytecode
+    from quompiler.construct.types import GateGrain
+    out = {}
+    names = []
+
+    def run_case(name, leaves, window, emit):
+        leaves = [l for l in leaves if isinstance(l, CtrlGate)]
+        root = Bytecode(np.eye(2), [Bytecode(CtrlGate(np.array(g.matrix()), g.controls(), g.qspace, g.phase())) for g in leaves])
+        opt = SlidingWindowCombiner(window=window, emit=GateGrain[emit])
+        res = opt.optimize(root)
+        after = [a.data for a in BytecodeIter(res) if a.is_leaf() and not a.skip and isinstance(a.data, CtrlGate)]
+        out.update(prefixed(name + "_before", pack_gates(leaves)))
+        out.update(prefixed(name + "_after", pack_gates(after)))
+        out[name + "_window"] = np.int64(window)
+        out[name + "_emit"] = np.str_(emit)
+        names.append(name)
+        print("opt", name, len(leaves), "->", len(after))
+
+    for tag, dim, emit, window in (("r4ct", 4, "CLIFFORD_T", 0), ("r4ug", 4, "UNIV_GATE", 0), ("r4pr", 4, "PRINCIPAL", 0),
+                                   ("r4cp", 4, "CTRL_PRUNED", 0), ("r8pr", 8, "PRINCIPAL", 0), ("r8pr_w2", 8, "PRINCIPAL", 2),
+                                   ("r8cp_w1", 8, "CTRL_PRUNED", 1), ("r8sg", 8, "SINGLET", 0)):
+        seed()
+        u = random_unitary(dim)
+        run_case(tag, compile_leaves(u, emit, optimize=False), window, emit)
+    seed()
+    run_case("cyc8ct", compile_leaves(cyclic_matrix(8, 1), "CLIFFORD_T", optimize=False), 0, "CLIFFORD_T")
+    T_, C1_, C0_ = QType.TARGET, QType.CONTROL1, QType.CONTROL0
+    q = [Qubit(i) for i in range(4)]
+    g1 = lambda g, t: CtrlGate(g, [T_], [q[t]])  # noqa: E731
+    cx = lambda c, t: CtrlGate(UnivGate.X, [C1_, T_], [q[c], q[t]])  # noqa: E731
+    hand = [g1(UnivGate.H, 0), g1(UnivGate.X, 0), g1(UnivGate.H, 0), g1(UnivGate.T, 1), g1(UnivGate.T, 1), g1(UnivGate.S, 2),
+            g1(UnivGate.S, 2), g1(UnivGate.X, 3), g1(UnivGate.X, 3), g1(UnivGate.I, 0), cx(0, 1), cx(0, 1), cx(1, 2), g1(UnivGate.H, 1),
+            cx(1, 2), g1(UnivGate.T, 0), g1(UnivGate.H, 3), g1(UnivGate.TD, 0), CtrlGate(UnivGate.Z, [C0_, T_], [q[2], q[3]]),
+            CtrlGate(UnivGate.Z, [T_, C0_], [q[3], q[2]]), g1(UnivGate.Y, 1), g1(UnivGate.H, 1), g1(UnivGate.Y, 1), g1(UnivGate.H, 1)]
+    for w in (0, 1, 2):
+        run_case(f"hand_w{w}", hand, w, "CLIFFORD_T")
+    run_case("hand_ug", hand, 0, "UNIV_GATE")
+    out["names"] = np.array(names)
+    np.savez_compressed(os.path.join(OUT, "optimizer.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "optimizer":
+        gen_optimizer()
+        sys.exit(0)
     gen_single_gates()
     gen_transforms()
     gen_index_math()
@@ -328,4 +376,5 @@ if __name__ == "__main__":
     gen_qft()
     gen_two_level()
     gen_qco()
+    gen_optimizer()
     print("done ->", os.path.abspath(OUT))
