@@ -19,10 +19,20 @@
 //   register-thread terms   -> two 16-entry tables over 4-bit chunks of the thread id (shared memory,
 //                              copied once per CTA), multiplied together
 //   register-global terms   -> per-tile scalars (one sincos per slot per tile, kept in shared memory)
-// so a QFT sweep with 8 Hadamards and ~200 controlled phases costs 8 butterflies + 8 phase ops.
+// so a QFT sweep with 6 Hadamards and ~150 controlled phases costs 6 butterflies + a few table lookups.
 //
 // A sweep may store the tile to a bit-permuted location of a second buffer (out of place): SWAP
 // gates then cost no arithmetic and no extra traffic.
+//
+// Launches whose every stage is "FFT shaped" (butterflies, each followed by phases that couple its bit
+// only to bits whose butterfly comes later, then the deferred phases) are rewritten by the host into
+// ONE op per stage (OP_FSTAGE) and run in a kernel image of their own (IMG_FFT) in which no amplitude
+// is carried in registers from one op to the next -- see fstage_math / to_fstages.  Everything else
+// runs in the generic interpreter images (IMG_LEAN, IMG_FULL).
+//
+// The per-op arithmetic (generic_op, fstage_op and below) is __host__ __device__: the same source is
+// interpreted on the host by qsv_hostcheck_fused (end of this file, test infrastructure) so that the
+// fusion pass can be checked against the oracle without a GPU.
 #include <stdlib.h>
 
 #include <algorithm>
