@@ -21,6 +21,7 @@ extern "C" {
 /* Build the fused plan for `gates` (one-target kinds only: QSV_DENSE1 / QSV_PERMX / QSV_DIAG1, same record
  * layout and pool as qsv_upload_program) over an n_bits register, tile size max_tile_bits (0 = default), and
  * run it on the HOST buffer `state` (2^n_bits interleaved complex values of `dtype`), in place.
+ * With state == NULL only the plan is built (n_bits up to 40): the counts below describe a full-size plan.
  * out_sweeps / out_fft_sweeps (may be NULL): number of fused launches / of those in the FFT-shaped image.
  * Returns a QSV_* status; on failure the message is copied to err[0..err_len). */
 int qsv_hostcheck_fused(int dtype, int n_bits, const qsv_gate_t* gates, uint64_t n_gates, const double* pool, uint64_t pool_elems,

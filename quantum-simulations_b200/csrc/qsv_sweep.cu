@@ -2179,8 +2179,9 @@ extern "C" int qsv_hostcheck_fused(int dtype, int n_bits, const qsv_gate_t* gate
     qsv_ctx ctx;  // never touches a device
     ctx.dtype = dtype;
     int rc = QSV_OK;
-    if ((dtype != QSV_C128 && dtype != QSV_C64) || n_bits < RB || n_bits > 22 || !state || (n_gates && !gates)) {
-        rc = qsv_fail(&ctx, QSV_E_INVALID, "hostcheck: bad arguments (n_bits must be %d..22)", RB);
+    // state == NULL: plan only (any register the planner accepts) -- the shape of a full-size plan can be asserted on a CPU
+    if ((dtype != QSV_C128 && dtype != QSV_C64) || n_bits < RB || n_bits > (state ? 22 : 40) || (n_gates && !gates)) {
+        rc = qsv_fail(&ctx, QSV_E_INVALID, "hostcheck: bad arguments (n_bits must be %d..22, up to 40 without a state)", RB);
     } else {
         for (uint64_t i = 0; i < n_gates && !rc; ++i) {
             const qsv_gate_t& g = gates[i];
@@ -2198,7 +2199,15 @@ extern "C" int qsv_hostcheck_fused(int dtype, int n_bits, const qsv_gate_t* gate
         ctx.has_program = true;
         rc = sweep_plan_build_host(&ctx, max_tile_bits, &plan);
     }
-    if (!rc) {
+    if (!rc && !state) {
+        uint64_t sweeps = 0, fft = 0;
+        for (auto& st : plan->steps) {
+            sweeps += st.fused;
+            fft += st.fused && st.img == IMG_FFT;
+        }
+        if (out_sweeps) *out_sweeps = sweeps;
+        if (out_fft_sweeps) *out_fft_sweeps = fft;
+    } else if (!rc) {
         rc = dtype == QSV_C128 ? hostcheck_run<double>(&ctx, plan, state, out_sweeps, out_fft_sweeps)
                                : hostcheck_run<float>(&ctx, plan, state, out_sweeps, out_fft_sweeps);
     }

@@ -43,3 +43,17 @@ def run_fused_on_host(recs, pool, state, n_bits, tile_bits=0, dtype=np.complex12
     if rc:
         raise RuntimeError(f"qsv_hostcheck_fused rc={rc}: {err.value.decode()}")
     return out, int(sweeps.value), int(fft.value)
+
+
+def plan_shape(recs, pool, n_bits, tile_bits=0):
+    """(n_sweeps, n_fft_sweeps) of the fused plan for a register of any size -- nothing is executed."""
+    fn = _load()
+    recs = np.ascontiguousarray(recs, dtype=_lib.GATE_DTYPE)
+    pool = np.ascontiguousarray(pool, dtype=np.complex128)
+    sweeps, fft = C.c_uint64(0), C.c_uint64(0)
+    err = C.create_string_buffer(512)
+    rc = fn(_lib.QSV_C128, n_bits, recs.ctypes.data, len(recs), pool.ctypes.data if pool.size else None, pool.size, tile_bits,
+            None, C.byref(sweeps), C.byref(fft), err, 512)
+    if rc:
+        raise RuntimeError(f"qsv_hostcheck_fused rc={rc}: {err.value.decode()}")
+    return int(sweeps.value), int(fft.value)

@@ -134,3 +134,34 @@ def test_hostcheck_rejects_bad_input():
     recs["target_bits"][0][0] = 9
     with pytest.raises(RuntimeError):
         run_fused_on_host(recs, prog.pool(), np.ones(32, dtype=complex), 5)
+
+
+@pytest.mark.parametrize("n,sweeps", [(24, 4), (28, 4), (30, 5), (34, 5)])
+def test_full_size_qft_plans(n, sweeps):
+    """Plan shape at BASELINE's sizes (nothing is executed): the whole QFT, final SWAP layer included, takes
+    ceil(n / 7) sweeps and every one of them is an FFT-shaped launch."""
+    from tests.hostcheck import plan_shape
+    prog = qft_program(n)
+    got, fft = plan_shape(prog.records(0), prog.pool(), n)
+    assert (got, fft) == (sweeps, sweeps)
+
+
+def test_sharded_qft34_local_segments_are_fft_shaped():
+    """The per-rank segments of QFT-34 over 8 GPUs (31 local bits): planner + localisation + fusion, plan only."""
+    from quantum_simulations_b200.sharded import localize_records, plan_sharded
+    from tests.hostcheck import plan_shape
+    n, g = 34, 3
+    prog = qft_program(n)
+    recs, pool = prog.records(0), prog.pool()
+    plan = plan_sharded(recs, n, g)
+    locals_ = [s for s in plan.steps if s[0] == "local"]
+    assert plan.n_exchanges == 3 and len(locals_) >= 2
+    total = fft = 0
+    for rank in (0, 5):
+        for li, s in enumerate(locals_):
+            lrecs, lpool = localize_records(recs, pool, s[1], plan.where_at[li], n - g, rank)
+            if len(lrecs):
+                a, b = plan_shape(lrecs, lpool, n - g)
+                total += a
+                fft += b
+    assert total > 0 and fft == total
