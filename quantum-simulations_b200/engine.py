@@ -68,6 +68,14 @@ class Engine:
         torch = _torch()
         return torch.empty(int(n_amps), dtype=_torch_dtype(self.np_dtype), device=f"cuda:{self.device}")
 
+    def from_host(self, array):
+        """Copy a host array to this engine's device as a flat tensor of the engine's amplitude type."""
+        flat = np.ascontiguousarray(array, dtype=self.np_dtype).reshape(-1)
+        return _torch().from_numpy(flat).to(f"cuda:{self.device}")
+
+    def synchronize(self):
+        _torch().cuda.synchronize(self.device)
+
     def stats(self) -> dict:
         s = QsvStats()
         check(self.lib.qsv_get_stats(self._ctx, C.byref(s)), self._ctx)

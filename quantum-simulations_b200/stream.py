@@ -257,9 +257,8 @@ class GpuChunkExecutor:
 
 def apply_stream(source, states, register=None, dtype=np.complex128, chunk_gates: int = 1 << 18, fuse=True, engine=None):
     """``engine.apply_circuit`` for programs too long to flatten in one piece: same result, bounded host memory."""
-    from .engine import _pow2_ceil_bits, _torch, get_engine
+    from .engine import _pow2_ceil_bits, get_engine
     eng = engine or get_engine(dtype)
-    torch = _torch()
     states = np.asarray(states)
     single = states.ndim == 1
     x = states.reshape(states.shape[0], -1)
@@ -272,11 +271,10 @@ def apply_stream(source, states, register=None, dtype=np.complex128, chunk_gates
         raise ValueError(f"state has {dim} rows, not a power of two")
     padded = np.zeros((dim, 1 << b), dtype=eng.np_dtype)
     padded[:, :batch] = x
-    dev = torch.from_numpy(padded.reshape(-1)).to(f"cuda:{eng.device}")
-    ex = GpuChunkExecutor(eng, dev, n + b, b, fuse)
+    ex = GpuChunkExecutor(eng, eng.from_host(padded), n + b, b, fuse)
     while first is not None:
         ex.apply(*first)
         first = next(chunks, None)
-    torch.cuda.synchronize(eng.device)
+    eng.synchronize()
     out = ex.state.view(dim, 1 << b).cpu().numpy()[:, :batch]
     return out[:, 0].copy() if single else np.ascontiguousarray(out)

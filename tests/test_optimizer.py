@@ -92,3 +92,31 @@ def test_optimiser_checked_on_the_gpu():
     phased = a + [qs.CtrlGate(np.exp(0.3j) * np.eye(2), [T], [q0])]
     assert not equal_on_device(a[::-1], phased[::-1])
     assert equal_on_device(a[::-1], phased[::-1], up_to_phase=True)
+
+
+def test_verify_plumbing_with_a_host_engine(monkeypatch):
+    """``optimize.verify`` above oracle-backed stand-ins (tests/host_engine.py): same calls as the GPU test."""
+    from quantum_simulations_b200.optimize import equal_on_device, optimize_checked
+    from tests import host_engine
+    host_engine.install(monkeypatch)
+    for name in ("r4ct", "r4pr", "hand_w0", "r8sg"):
+        before = unpack_gates(D, name + "_before")
+        root = Bytecode(np.eye(2), [Bytecode(g) for g in before])
+        opt = SlidingWindowCombiner(window=int(D[name + "_window"]), emit=qs.GateGrain[str(D[name + "_emit"])])
+        out = optimize_checked(root, opt)
+        after = [a.data for a in BytecodeIter(out) if a.is_leaf() and not a.skip]
+        assert len(after) == len(unpack_gates(D, name + "_after"))
+    a = unpack_gates(D, "hand_w0_before")
+    q0 = a[0].qspace[0]
+    broken = a + [qs.CtrlGate(qs.UnivGate.T, [T], [q0])]
+    info = {}
+    assert not equal_on_device(a[::-1], broken[::-1], info=info) and info["violations"] > 0
+    phased = a + [qs.CtrlGate(np.exp(0.3j) * np.eye(2), [T], [q0])]
+    assert not equal_on_device(a[::-1], phased[::-1])
+    assert equal_on_device(a[::-1], phased[::-1], up_to_phase=True)
+    with pytest.raises(AssertionError):
+        class Bad:
+            def optimize(self, root):
+                root.children.pop()
+                return root
+        optimize_checked(Bytecode(np.eye(2), [Bytecode(g) for g in a]), Bad())

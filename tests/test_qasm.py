@@ -154,3 +154,34 @@ def test_text_evaluated_by_the_cuda_engine():
     got = b.finish().unitary()
     want = orc.simulate(gates, reg, np.eye(16, dtype=np.complex128))
     assert np.abs(got - want).max() < 1e-10
+
+
+def test_unitary_plumbing_with_a_host_engine(monkeypatch):
+    """``QasmCircuit.unitary`` above an oracle-backed ``simulate_columns`` (tests/host_engine.py): the same calls the GPU
+    test makes, so its argument plumbing (ancilla handling, qubit order) is exercised on a CPU box too."""
+    from tests import host_engine
+    host_engine.install(monkeypatch)
+    d = load("streams")
+    for name in ("cfg1", "cfg2s"):
+        b = QasmBuilder()
+        for g in unpack_gates(d, name)[::-1]:
+            b.build_gate(g)
+        assert np.abs(b.finish().unitary(drop_ancilla=True) - d[f"{name}_value"]).max() < 1e-10
+    gates = _random_one_target_gates(4, 40, 5)
+    reg = [qs.Qubit(i) for i in range(4)]
+    b = QasmBuilder()
+    b.register(reg)
+    for g in gates:
+        b.build_gate(g)
+    want = orc.simulate(gates, reg, np.eye(16, dtype=np.complex128))
+    assert np.abs(b.finish().unitary() - want).max() < 1e-10
+    order = [reg[3], reg[1], reg[0], reg[2]]
+    assert np.abs(b.finish().unitary(order) - orc.simulate(gates, order, np.eye(16, dtype=np.complex128))).max() < 1e-10
+    # ancillas kept as ordinary qubits: the full 16x16 operator of a 3+1 register
+    gs = [qs.CtrlGate(qs.UnivGate.H, [T], [qs.Qubit(0)]), qs.CtrlGate(qs.UnivGate.X, [C1, T], [qs.Qubit(0), qs.Qubit(9, True)])]
+    b = QasmBuilder()
+    for g in gs:
+        b.build_gate(g)
+    full = b.finish().unitary()
+    assert full.shape == (4, 4) and abs(full[0b11, 0] - 1 / np.sqrt(2)) < 1e-12
+    assert b.finish().unitary(drop_ancilla=True).shape == (2, 2)

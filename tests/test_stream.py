@@ -159,3 +159,64 @@ def test_apply_stream_on_the_gpu_equals_apply_circuit():
         assert np.abs(got - want).max() < 1e-10
     ref = orc.simulate(gates, reg, x)
     assert np.abs(want - ref).max() < 1e-10
+
+
+class _HostEngine:
+    """Stand-in for ``engine.Engine`` with the oracle behind it (TEST ONLY): lets the chunk executor's bookkeeping --
+    buffer ping-pong, spare allocation, the fall-back when the fusion pass refuses a chunk -- run on a CPU box."""
+
+    def __init__(self, refuse_fuse_every=0):
+        import torch
+        self.torch = torch
+        self.np_dtype = np.dtype(np.complex128)
+        self.device = 0
+        self.calls = []
+        self.refuse = refuse_fuse_every
+        self.n_fuse = 0
+
+    def from_host(self, array):
+        return self.torch.from_numpy(np.ascontiguousarray(array, dtype=self.np_dtype).reshape(-1).copy())
+
+    def empty(self, n):
+        return self.torch.empty(int(n), dtype=self.torch.complex128)
+
+    def synchronize(self):
+        pass
+
+    def upload_records(self, recs, pool, n_bits, batch_bits=0):
+        self.prog = (recs.copy(), pool.copy(), n_bits)
+        self.fused = False
+
+    def fuse(self, max_tile_bits=0):
+        from quantum_simulations_b200._lib import QsvError
+        self.n_fuse += 1
+        if self.refuse and self.n_fuse % self.refuse == 0:
+            raise QsvError("unsupported: refused by the test")
+        self.fused = True
+        return 1
+
+    def run(self, state, spare=None):
+        recs, pool, n_bits = self.prog
+        # like the device: a fused plan may leave its result in the spare buffer
+        out = spare if (self.fused and spare is not None and len(self.calls) % 2 == 0) else state
+        if out is not state:
+            out.copy_(state)
+        orc.run_records(recs, pool, out.numpy(), n_bits)
+        self.calls.append(self.fused)
+        return out
+
+
+@pytest.mark.parametrize("refuse", [0, 2])
+def test_apply_stream_bookkeeping_with_a_host_engine(refuse):
+    from quantum_simulations_b200.stream import apply_stream
+    n = 7
+    gates = [g for g in _random_gates(n, 150, 21) if len([c for c in g.controls() if int(c) in (1, 8)]) == 1]
+    reg = [qs.Qubit(i) for i in range(n)]
+    x = np.stack([random_state(1 << n) for _ in range(3)], axis=1)
+    eng = _HostEngine(refuse)
+    got = apply_stream(gates, x, reg, chunk_gates=16, engine=eng)
+    want = orc.simulate(gates, reg, x)
+    assert got.shape == x.shape and np.abs(got - want).max() < 1e-12
+    assert len(eng.calls) == -(-len(gates) // 16) and (all(eng.calls) if not refuse else not all(eng.calls))
+    one = apply_stream(gates, x[:, 0], reg, chunk_gates=1 << 18, engine=_HostEngine())
+    assert one.shape == (1 << n,) and np.abs(one - want[:, 0]).max() < 1e-12
