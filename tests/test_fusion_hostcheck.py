@@ -165,3 +165,18 @@ def test_sharded_qft34_local_segments_are_fft_shaped():
                 total += a
                 fft += b
     assert total > 0 and fft == total
+
+
+def test_batched_qft_config3_shape_and_semantics():
+    """BASELINE config 3 (QFT-24 on 64 states, batch innermost = 6 low index bits no gate touches): the plan at full size
+    is 4 FFT-shaped sweeps; at small size every column of the batch comes out as the inverse FFT of its input."""
+    from tests.hostcheck import plan_shape
+    p = qft_program(24)
+    assert plan_shape(p.records(6), p.pool(), 30) == (4, 4)
+    n, b = 10, 3
+    p = qft_program(n)
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((1 << n, 1 << b)) + 1j * rng.standard_normal((1 << n, 1 << b))
+    x /= np.linalg.norm(x, axis=0)
+    got, _, fft = run_fused_on_host(p.records(b), p.pool(), x.reshape(-1), n + b, 11)
+    assert fft >= 1 and np.abs(got.reshape(1 << n, 1 << b) - np.fft.ifft(x, axis=0, norm="ortho")).max() < 1e-12
