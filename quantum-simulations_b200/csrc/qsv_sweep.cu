@@ -31,8 +31,8 @@
 // runs in the generic interpreter images (IMG_LEAN, IMG_FULL).
 //
 // The per-op arithmetic (generic_op, fstage_op and below) is __host__ __device__: the same source is
-// interpreted on the host by qsv_hostcheck_fused (end of this file, test infrastructure) so that the
-// fusion pass can be checked against the oracle without a GPU.
+// (qsv_sweep_ops.cuh) is interpreted on the host by qsv_hostcheck_fused (qsv_hostcheck.cu, test infrastructure)
+// so that the fusion pass can be checked against the oracle without a GPU.
 #include <stdlib.h>
 
 #include <algorithm>
@@ -41,503 +41,7 @@
 #include <map>
 
 #include "qsv_common.cuh"
-
-#define KMAX 12          // max local (tile) bits: 2^12 x 16 B = 64 KB of shared memory
-#define RB 4             // register bits per stage
-#define NREG 16
-#define MAX_OPS 320      // ops per launch (kernel parameter space, 32 KB limit)
-#define MAX_GSLOT 48     // per-tile phase scalars per launch (double-buffered in shared memory by tile parity)
-#define MAX_TAB 384      // double2 entries of phase tables per launch (6 KB of shared memory)
-#define PARK_WORDS 3     // 64-bit per-thread tile-copy constants parked in shared memory (registers are at the 3-CTA/SM cap)
-#define SWEEP_SMEM(amp_bytes, k, threads) \
-    (2 * ((size_t)(amp_bytes) << (k)) + (2 * MAX_GSLOT + MAX_TAB) * sizeof(double2) + (size_t)PARK_WORDS * (threads) * sizeof(uint64_t))
-#define TSLOT_LEN 32     // one thread-phase slot = 2 chunks x 16 entries
-#define MAX_SEG 12
-
-enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_W = 4, OP_TWID = 5, OP_HADD = 6, OP_HW = 7, OP_FSTAGE = 8 };
-// Dispatch codes (SwOp::type as stored): the host resolves op kind, target register bit, real/complex
-// and controlled/uncontrolled into ONE small integer so that the device decodes an op with a single
-// jump-table branch.
-enum : uint8_t {
-    // codes 0..18 are the lean kernel's set and are dense so that its switch compiles to one jump table
-    DC_STAGE = 0,
-    DC_DENSE_REAL_NC = 1,    // +tgt (4 codes each); NC = no control of any kind
-    DC_DENSE_CPLX_NC = 5,
-    DC_HADD = 9,             // +tgt: unnormalised Hadamard butterfly (a0+a1, a0-a1); the 1/sqrt2 is folded into a later OP_TWID
-    DC_W = 13,               // register-register phase table: v[j] *= W[j]
-    DC_TWID = 14,            // deferred per-register-bit phases (thread / tile dependent) + thread-wide factor + real scale
-    DC_HW = 15,              // +tgt: unnormalised Hadamard butterfly immediately followed by a register-register phase table
-    DC_FSTAGE = 19,          // +shape (10 codes): a whole register stage of the "FFT shape" as ONE straight-line op (see
-                             // fstage_math); runs only in the IMG_FFT kernel image, whose launches hold nothing else
-    DC_FIRST_FULL = 29,      // codes from here on exist only in the full kernel image
-    DC_DENSE_CPLX_C = 29,    // +tgt: controlled (register / thread / tile controls)
-    DC_PERMX = 33,           // +tgt
-    DC_MPHASE = 37,
-};
-#define NONE16 0xFFFFu
-#define NONE32 0xFFFFFFFFu
-
-struct __align__(16) SwOp {  // 96 bytes = 6 x 16 B, read into registers with six 128-bit constant loads
-    uint8_t type, tgt, rmask, rval;  // tgt: register bit (0..3); rmask/rval: control over the register index
-    uint16_t lmask, lval;            // control over the thread's local bits (register bits excluded)
-    uint64_t gmask, gval;            // control over the tile id
-    union {
-        double m[8];                 // OP_DENSE: 2x2 (re,im) row-major; OP_MPHASE: m[0..1] = factor
-        struct {                     // OP_STAGE
-            uint16_t roffsw[NREG];   // swizzled shared-memory slot offset of register j
-            uint8_t rpos[RB];        // local bit positions of the register bits, ascending
-            uint8_t flags;
-        } st;
-        struct {                     // OP_W
-            uint16_t w_off;          // W table offset (16 entries) in the shared tables
-            uint16_t wmask;          // registers j with W[j] != 1
-        } w;
-        struct {                     // OP_TWID
-            double scale;            // real factor applied to every register (1.0 = none)
-            uint16_t tslot[RB + 1];  // thread-phase slot (offset into the shared tables) per listed bit, [RB] = thread-wide factor
-            uint16_t gslot[RB + 1];  // per-tile scalar slot per listed bit, [RB] = thread-wide factor
-            uint8_t abit[RB];        // register bit index of each listed slot
-            uint8_t n_active;
-        } tw;
-        struct {                     // OP_FSTAGE: the first 33 bytes are laid out exactly like `tw`
-            double scale;
-            uint16_t tslot[RB + 1];
-            uint16_t gslot[RB + 1];
-            uint8_t abit[RB];
-            uint8_t n_active;
-            uint8_t hmask;           // @33: number of butterflies NH: register bits 3, 2, ... (3 - NH + 1) get one, in that order
-            uint8_t flags;           // @34: 1 = per-bit deferred phases, 2 = thread-wide factor / scale, 4 = that factor is complex
-            uint8_t pad_;
-            uint16_t w_off[3];       // @36: 16-entry phase table applied right after the butterfly of bit 3 / 2 / 1 (always valid in
-                                     //      the shapes with tables); it touches only registers with bit A set, indexed by the bits below A
-            uint8_t rpos[RB];        // @42: local bit positions of the register bits, ascending (for the thread-index expansion)
-            uint16_t boff[RB];       // @46: swizzled shared-memory slot offset of register bit q (register bits are NOT in position order)
-        } fs;
-    };
-};
-static_assert(sizeof(SwOp) == 96, "SwOp layout");
-static_assert(offsetof(SwOp, tw) == 24 && offsetof(SwOp, fs.hmask) == 24 + 33 && offsetof(SwOp, fs.w_off) == 24 + 36 &&
-                  offsetof(SwOp, fs.rpos) == 24 + 42 && offsetof(SwOp, fs.boff) == 24 + 46 && offsetof(SwOp, tw.abit) == offsetof(SwOp, fs.abit),
-              "OP_FSTAGE payload offsets are hard-coded in the kernel");
-
-struct SegMap {  // x -> sum_s ((x >> src) & ((1<<len)-1)) << dst
-    uint8_t n, src[MAX_SEG], len[MAX_SEG], dst[MAX_SEG];
-};
-
-struct SegMap64 {  // same over up to 64 source bits (tile id -> global offset)
-    uint8_t n, src[48], len[48], dst[48];
-};
-
-struct SweepDesc {
-    int n_bits, k, n_ops, n_gslots, n_glob, tb;  // tb = log2(blockDim)
-    uint32_t gtab_off;              // double2 units: per per-tile scalar slot, g_chunks x 16 entries
-    int g_chunks;                   // ceil(n_glob / 4), at least 1
-    SegMap in_loc, out_loc, st_enum;  // local index -> physical offset (load / store), store enumeration
-    SegMap64 in_glob, out_glob;     // tile id -> physical base offset (load / store)
-    // All index maps are bitwise-linear, so the tile copy splits every address into a per-thread part
-    // (computed once per kernel from the maps above) and a per-slot part (below, host-computed):
-    // slot i of thread tid handles local index  tid | (i << tb)  on load and  st_enum(tid | (i << tb))  on store.
-    uint64_t ld_goff[NREG], st_goff[NREG];  // global offset contributed by slot i
-    uint16_t ld_soff[NREG], st_soff[NREG];  // swizzled shared-memory slot contributed by slot i
-    // When the first (last) stage keeps only high local bits in registers, the tile is loaded
-    // (stored) straight into (from) that stage's register layout and skips one trip through
-    // shared memory: slot j is then register j and the thread part is the stage's base index.
-    uint8_t direct_load, direct_store;
-    uint8_t first_rpos[RB], last_rpos[RB];
-    uint32_t tab_off, tab_len;              // shared phase tables: aux offset / length in double2 units
-    // Fused exchange (multi-GPU): when xg > 0 the store does not go to `dst` but straight into the peers' buffers over
-    // NVLink -- the top xg bits of the (permuted) output index select the destination rank, and this rank's id takes
-    // their place in the address there.  That is the all-to-all "global bits <-> top local bits" done by the sweep's
-    // own stores: no NCCL call and no extra pass over the shard.
-    int xg, xrank;
-    uint64_t peer[8];                       // device address of every rank's destination buffer (peer-mapped)
-};
-
-struct SweepParams {
-    SweepDesc d;
-    SwOp ops[MAX_OPS];
-};
-static_assert(sizeof(SweepParams) < 32700, "kernel parameter space");
-
-__host__ __device__ __forceinline__ uint32_t seg_apply(uint32_t x, const SegMap& m) {
-    uint32_t r = 0;
-    for (int s = 0; s < m.n; ++s) r |= ((x >> m.src[s]) & ((1u << m.len[s]) - 1u)) << m.dst[s];
-    return r;
-}
-__host__ __device__ __forceinline__ uint64_t seg_apply64(uint32_t x, const SegMap& m) {
-    uint64_t r = 0;
-    for (int s = 0; s < m.n; ++s) r |= (uint64_t)((x >> m.src[s]) & ((1u << m.len[s]) - 1u)) << m.dst[s];
-    return r;
-}
-__host__ __device__ __forceinline__ uint64_t seg_apply64x(uint64_t x, const SegMap64& m) {
-    uint64_t r = 0;
-    for (int s = 0; s < m.n; ++s) r |= ((x >> m.src[s]) & ((1ull << m.len[s]) - 1ull)) << m.dst[s];
-    return r;
-}
-__host__ __device__ __forceinline__ uint32_t swz(uint32_t l) { return l ^ (((l >> 3) ^ (l >> 6) ^ (l >> 9)) & 7u); }
-
-// An op held in registers: header words + 64-byte payload (all accesses statically indexed).
-struct OpR {
-    uint32_t w0, w1;       // w0 = type | tgt<<8 | rmask<<16 | rval<<24 ; w1 = lmask | lval<<16
-    uint64_t gmask, gval;
-    uint64_t p[8];         // payload: matrix doubles / stage table / run slots
-    __host__ __device__ __forceinline__ uint32_t type() const { return w0 & 0xFFu; }
-    __host__ __device__ __forceinline__ uint32_t tgt() const { return (w0 >> 8) & 0xFFu; }
-    __host__ __device__ __forceinline__ uint32_t rmask() const { return (w0 >> 16) & 0xFFu; }
-    __host__ __device__ __forceinline__ uint32_t rval() const { return w0 >> 24; }
-    __host__ __device__ __forceinline__ uint32_t lmask() const { return w1 & 0xFFFFu; }
-    __host__ __device__ __forceinline__ uint32_t lval() const { return w1 >> 16; }
-    __host__ __device__ __forceinline__ double m(int i) const {
-        double d;
-        memcpy(&d, &p[i], sizeof(d));  // (bit cast; compiles to nothing on the device)
-        return d;
-    }
-    // OP_STAGE payload: roffsw[16] (u16) then rpos[4] (u8)
-    __host__ __device__ __forceinline__ uint32_t roffsw(int j) const { return (uint32_t)(p[j >> 2] >> (16 * (j & 3))) & 0xFFFFu; }
-    __host__ __device__ __forceinline__ uint32_t rpos(int q) const { return (uint32_t)(p[4] >> (8 * q)) & 0xFFu; }
-    // generic little-endian field access into the payload (offsets are compile-time constants)
-    __host__ __device__ __forceinline__ uint32_t u16_at(int off) const { return (uint32_t)(p[off >> 3] >> (8 * (off & 7))) & 0xFFFFu; }
-    __host__ __device__ __forceinline__ uint32_t u8_at(int off) const { return (uint32_t)(p[off >> 3] >> (8 * (off & 7))) & 0xFFu; }
-    // OP_W payload: w_off @0, wmask @2.  OP_TWID payload: scale @0, tslot[s] @8+2s, gslot[s] @8+2(RB+1)+2s, abit[s] @8+4(RB+1)+s, n_active after
-    __host__ __device__ __forceinline__ uint32_t tw_tslot(int s_) const { return u16_at(8 + 2 * s_); }
-    __host__ __device__ __forceinline__ uint32_t tw_gslot(int s_) const { return u16_at(8 + 2 * (RB + 1) + 2 * s_); }
-    __host__ __device__ __forceinline__ uint32_t tw_abit(int s_) const { return u8_at(8 + 4 * (RB + 1) + s_); }
-    __host__ __device__ __forceinline__ uint32_t tw_n() const { return u8_at(8 + 4 * (RB + 1) + RB); }
-};
-
-__host__ __device__ __forceinline__ OpR fetch_op(const SwOp* __restrict__ ops, int i) {
-    const ulonglong2* w = reinterpret_cast<const ulonglong2*>(ops + i);
-    const ulonglong2 a = w[0], b = w[1], c = w[2], d = w[3], e = w[4], f = w[5];
-    OpR r;
-    r.w0 = (uint32_t)a.x;
-    r.w1 = (uint32_t)(a.x >> 32);
-    r.gmask = a.y;
-    r.gval = b.x;
-    r.p[0] = b.y; r.p[1] = c.x; r.p[2] = c.y; r.p[3] = d.x; r.p[4] = d.y; r.p[5] = e.x; r.p[6] = e.y; r.p[7] = f.x;
-    return r;
-}
-
-template <typename C, bool CTRL, int A>
-__host__ __device__ __forceinline__ void op_dense(C (&v)[NREG], const OpR& op, bool tpred) {
-    typedef decltype(v[0].x) R;
-    const C m00 = cmake<C, R>((R)op.m(0), (R)op.m(1)), m01 = cmake<C, R>((R)op.m(2), (R)op.m(3));
-    const C m10 = cmake<C, R>((R)op.m(4), (R)op.m(5)), m11 = cmake<C, R>((R)op.m(6), (R)op.m(7));
-    const uint32_t rm = op.rmask(), rv = op.rval();
-#pragma unroll
-    for (int j0 = 0; j0 < NREG; ++j0)
-        if (!(j0 & (1 << A))) {
-            const int j1 = j0 | (1 << A);
-            if (!CTRL || (((j0 & rm) == rv) && tpred)) {
-                const C a0 = v[j0], a1 = v[j1];
-                v[j0] = cfma(m01, a1, cmul(m00, a0));
-                v[j1] = cfma(m11, a1, cmul(m10, a0));
-            }
-        }
-}
-
-// real-entry matrices (H, rotations about y, ...): half the multiplies
-template <typename C, bool CTRL, int A>
-__host__ __device__ __forceinline__ void op_dense_real(C (&v)[NREG], const OpR& op, bool tpred) {
-    typedef decltype(v[0].x) R;
-    const R m00 = (R)op.m(0), m01 = (R)op.m(2), m10 = (R)op.m(4), m11 = (R)op.m(6);
-    const uint32_t rm = op.rmask(), rv = op.rval();
-#pragma unroll
-    for (int j0 = 0; j0 < NREG; ++j0)
-        if (!(j0 & (1 << A))) {
-            const int j1 = j0 | (1 << A);
-            if (!CTRL || (((j0 & rm) == rv) && tpred)) {
-                const C a0 = v[j0], a1 = v[j1];
-                v[j0].x = fma(m01, a1.x, m00 * a0.x);
-                v[j0].y = fma(m01, a1.y, m00 * a0.y);
-                v[j1].x = fma(m11, a1.x, m10 * a0.x);
-                v[j1].y = fma(m11, a1.y, m10 * a0.y);
-            }
-        }
-}
-
-template <typename C, int A>
-__host__ __device__ __forceinline__ void op_permx(C (&v)[NREG], const OpR& op, bool tpred) {
-    const uint32_t rm = op.rmask(), rv = op.rval();
-#pragma unroll
-    for (int j0 = 0; j0 < NREG; ++j0)
-        if (!(j0 & (1 << A))) {
-            const int j1 = j0 | (1 << A);
-            if (((j0 & rm) == rv) && tpred) {
-                const C t = v[j0];
-                v[j0] = v[j1];
-                v[j1] = t;
-            }
-        }
-}
-
-__host__ __device__ __forceinline__ uint32_t expand_rb(uint32_t g, const uint8_t* rpos) {
-#pragma unroll
-    for (int q = 0; q < RB; ++q) {
-        const uint32_t p = rpos[q];
-        g = ((g >> p) << (p + 1)) | (g & ((1u << p) - 1u));
-    }
-    return g;
-}
-
-// unnormalised Hadamard butterfly on register bit A: (a0, a1) -> (a0 + a1, a0 - a1)
-template <typename C, int A>
-__host__ __device__ __forceinline__ void op_hadd(C (&v)[NREG]) {
-#pragma unroll
-    for (int j0 = 0; j0 < NREG; ++j0)
-        if (!(j0 & (1 << A))) {
-            const int j1 = j0 | (1 << A);
-            const C a0 = v[j0], a1 = v[j1];
-            v[j0].x = a0.x + a1.x;
-            v[j0].y = a0.y + a1.y;
-            v[j1].x = a0.x - a1.x;
-            v[j1].y = a0.y - a1.y;
-        }
-}
-
-// v[j] *= e for every register j that has bit A set
-template <typename C, int A>
-__host__ __device__ __forceinline__ void mul_bit(C (&v)[NREG], const double2 e) {
-    typedef decltype(v[0].x) R;
-    const C ee = cmake<C, R>((R)e.x, (R)e.y);
-#pragma unroll
-    for (int j = 0; j < NREG; ++j)
-        if (j & (1 << A)) v[j] = cmul(v[j], ee);
-}
-
-// Deferred phases of a stage (OP_TWID and the tail of OP_FSTAGE): thread-wide complex factor / real scale, then one factor per
-// register bit -- each the product of a per-tile scalar (smE) and two 16-entry tables over the 4-bit chunks of the thread id.
-template <typename C, typename R>
-__host__ __device__ __forceinline__ void twid_math(C (&v)[NREG], const OpR& op, const double2* __restrict__ smT, const double2* __restrict__ smE,
-                                          const uint32_t tid) {
-    const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
-    const double scale = op.m(0);
-    const uint32_t ts0 = op.tw_tslot(RB), gs0 = op.tw_gslot(RB);
-    if (ts0 != NONE16 || gs0 != NONE16) {  // thread-wide complex factor (times the scale)
-        double2 c0 = make_double2(scale, 0.0);
-        if (gs0 != NONE16) {
-            const double2 g0 = smE[gs0];
-            c0 = make_double2(scale * g0.x, scale * g0.y);
-        }
-        if (ts0 != NONE16) c0 = cmul(c0, cmul(smT[ts0 + c_lo], smT[ts0 + c_hi]));
-        const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
-#pragma unroll
-        for (int j = 0; j < NREG; ++j) v[j] = cmul(v[j], cc);
-    } else if (scale != 1.0) {
-        const R sc = (R)scale;
-#pragma unroll
-        for (int j = 0; j < NREG; ++j) {
-            v[j].x *= sc;
-            v[j].y *= sc;
-        }
-    }
-    // slot s_ holds the factor of register bit s_ (abit[s_] == 0xFF: nothing pending on that bit)
-#define TWID_BIT(B)                                                             \
-    if (op.tw_abit(B) != 0xFFu) {                                               \
-        double2 e = make_double2(1.0, 0.0);                                     \
-        const uint32_t gsl = op.tw_gslot(B), tsl = op.tw_tslot(B);              \
-        if (gsl != NONE16) e = smE[gsl];                                        \
-        if (tsl != NONE16) e = cmul(e, cmul(smT[tsl + c_lo], smT[tsl + c_hi])); \
-        mul_bit<C, B>(v, e);                                                    \
-    }
-    TWID_BIT(0)
-    TWID_BIT(1)
-    TWID_BIT(2)
-    TWID_BIT(3)
-#undef TWID_BIT
-}
-
-// OP_FSTAGE arithmetic, one straight line per SHAPE so that no branch ever joins two register allocations:
-//   NH    butterflies on the TOP NH register bits, in the order 3, 2, ... (the host relabels register bits to make it so);
-//   HAS_W each butterfly on bit A > 0 is followed by its register-register phase table, which multiplies only registers
-//         with bit A set and depends only on the register bits below A (the internal twiddles of a radix-16 FFT
-//         butterfly): 7 + 2*3 + 4*1 multiplies, statically indexed (absent tables point at an all-ones table);
-//   then the deferred phases: unconditionally on the NH butterfly bits (absent factors point at all-ones slots),
-//   behind a uniform branch for the thread-wide factor / scale and for the other register bits (rare).
-template <typename C, typename R, int B>
-__host__ __device__ __forceinline__ void twid_bit_always(C (&v)[NREG], const OpR& op, const double2* __restrict__ smT, const double2* __restrict__ smE,
-                                                const uint32_t c_lo, const uint32_t c_hi) {
-    const uint32_t gsl = op.tw_gslot(B), tsl = op.tw_tslot(B);
-    const double2 e = cmul(smE[gsl], cmul(smT[tsl + c_lo], smT[tsl + c_hi]));
-    mul_bit<C, B>(v, e);
-}
-template <typename C, typename R, int B>
-__host__ __device__ __forceinline__ void twid_bit_maybe(C (&v)[NREG], const OpR& op, const double2* __restrict__ smT, const double2* __restrict__ smE,
-                                               const uint32_t c_lo, const uint32_t c_hi) {
-    if (op.tw_abit(B) != 0xFFu) twid_bit_always<C, R, B>(v, op, smT, smE, c_lo, c_hi);
-}
-
-template <typename C, typename R, int NH, bool HAS_W>
-__host__ __device__ __forceinline__ void fstage_math(C (&v)[NREG], const OpR& op, const double2* __restrict__ smT, const double2* __restrict__ smE,
-                                            const uint32_t tid) {
-    if constexpr (NH >= 1) {
-        op_hadd<C, 3>(v);
-        if constexpr (HAS_W) {
-            const double2* w = smT + op.u16_at(36) + 8;
-#pragma unroll
-            for (int m = 1; m < 8; ++m) {
-                const double2 e = w[m];
-                v[8 + m] = cmul(v[8 + m], cmake<C, R>((R)e.x, (R)e.y));
-            }
-        }
-    }
-    if constexpr (NH >= 2) {
-        op_hadd<C, 2>(v);
-        if constexpr (HAS_W) {
-            const double2* w = smT + op.u16_at(38) + 4;
-#pragma unroll
-            for (int m = 1; m < 4; ++m) {
-                const double2 e = w[m];
-                const C ee = cmake<C, R>((R)e.x, (R)e.y);
-                v[4 + m] = cmul(v[4 + m], ee);
-                v[12 + m] = cmul(v[12 + m], ee);
-            }
-        }
-    }
-    if constexpr (NH >= 3) {
-        op_hadd<C, 1>(v);
-        if constexpr (HAS_W) {
-            const double2 e = smT[op.u16_at(40) + 3];
-            const C ee = cmake<C, R>((R)e.x, (R)e.y);
-            v[3] = cmul(v[3], ee);
-            v[7] = cmul(v[7], ee);
-            v[11] = cmul(v[11], ee);
-            v[15] = cmul(v[15], ee);
-        }
-    }
-    if constexpr (NH >= 4) op_hadd<C, 0>(v);
-    // ---- deferred phases ----
-    const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
-    const uint32_t fl = op.u8_at(34);
-    if (fl & 2u) {  // thread-wide complex factor and / or real scale
-        const double scale = op.m(0);
-        const uint32_t ts0 = op.tw_tslot(RB), gs0 = op.tw_gslot(RB);
-        if (fl & 4u) {
-            const double2 g0 = smE[gs0];
-            const double2 c0 = cmul(make_double2(scale * g0.x, scale * g0.y), cmul(smT[ts0 + c_lo], smT[ts0 + c_hi]));
-            const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
-#pragma unroll
-            for (int j = 0; j < NREG; ++j) v[j] = cmul(v[j], cc);
-        } else {
-            const R sc = (R)scale;
-#pragma unroll
-            for (int j = 0; j < NREG; ++j) {
-                v[j].x *= sc;
-                v[j].y *= sc;
-            }
-        }
-    }
-    if (fl & 1u) {
-        if constexpr (NH >= 1) twid_bit_always<C, R, 3>(v, op, smT, smE, c_lo, c_hi); else twid_bit_maybe<C, R, 3>(v, op, smT, smE, c_lo, c_hi);
-        if constexpr (NH >= 2) twid_bit_always<C, R, 2>(v, op, smT, smE, c_lo, c_hi); else twid_bit_maybe<C, R, 2>(v, op, smT, smE, c_lo, c_hi);
-        if constexpr (NH >= 3) twid_bit_always<C, R, 1>(v, op, smT, smE, c_lo, c_hi); else twid_bit_maybe<C, R, 1>(v, op, smT, smE, c_lo, c_hi);
-        if constexpr (NH >= 4) twid_bit_always<C, R, 0>(v, op, smT, smE, c_lo, c_hi); else twid_bit_maybe<C, R, 0>(v, op, smT, smE, c_lo, c_hi);
-    }
-}
-
-// One whole OP_FSTAGE: shared memory -> registers -> fstage_math -> shared memory, or straight to HBM when this is the
-// launch's last op and the stage's register bits allow a coalesced store.  Returns true when it stored to HBM.
-template <typename C, typename R, int NH, bool HAS_W>
-__host__ __device__ __forceinline__ bool fstage_op(const OpR& op, C* __restrict__ tile, const double2* __restrict__ smT,
-                                          const double2* __restrict__ smE, const uint32_t tid, const bool active, const bool to_hbm,
-                                          C* __restrict__ dst, const uint64_t gbs, const uint64_t (&st_goff)[NREG]) {
-    // (threads beyond the tile's groups -- tiles smaller than a warp's worth -- redo thread 0's loads and never store:
-    // an unconditional load keeps the registers defined on every path, which the register allocator needs)
-    uint32_t bl = active ? tid : 0u;
-#pragma unroll
-    for (int q = 0; q < RB; ++q) {
-        const uint32_t pz = op.u8_at(42 + q);
-        bl = ((bl >> pz) << (pz + 1)) | (bl & ((1u << pz) - 1u));
-    }
-    // swizzle and register offsets are XOR-linear: slot of register j = slot of register 0 ^ offsets of j's set bits
-    uint32_t a[NREG];
-    a[0] = swz(bl);
-#pragma unroll
-    for (int j = 1; j < NREG; ++j) a[j] = a[j & (j - 1)] ^ op.u16_at(46 + 2 * ((j & 1) ? 0 : (j & 2) ? 1 : (j & 4) ? 2 : 3));
-    C w[NREG];
-#pragma unroll
-    for (int j = 0; j < NREG; ++j) w[j] = tile[a[j]];
-    fstage_math<C, R, NH, HAS_W>(w, op, smT, smE, tid);
-    if (to_hbm) {
-        if (active) {
-#pragma unroll
-            for (int j = 0; j < NREG; ++j) dst[gbs | st_goff[j]] = w[j];
-        }
-        return true;
-    }
-    if (active) {
-        // the 16 slot numbers are rebuilt from slot 0 (15 XORs) rather than kept in registers across the arithmetic:
-        // the opaque copy stops the compiler from re-using the ones computed for the load
-        uint32_t b[NREG];
-        b[0] = a[0];
-#ifdef __CUDA_ARCH__
-        asm volatile("" : "+r"(b[0]));
-#endif
-#pragma unroll
-        for (int j = 1; j < NREG; ++j) b[j] = b[j & (j - 1)] ^ op.u16_at(46 + 2 * ((j & 1) ? 0 : (j & 2) ? 1 : (j & 4) ? 2 : 3));
-#pragma unroll
-        for (int j = 0; j < NREG; ++j) tile[b[j]] = w[j];
-    }
-#ifdef __CUDA_ARCH__
-    __syncthreads();
-#endif
-    return false;
-}
-
-// One op of the generic interpreter applied to a thread's 16 registers (everything but the stage changes).
-template <typename C, typename R, bool LEAN>
-__host__ __device__ __forceinline__ void generic_op(C (&v)[NREG], const OpR& op, const uint32_t type, const bool tpred,
-                                                    const double2* __restrict__ smT, const double2* __restrict__ smE, const uint32_t tid) {
-#define DENSE_CASES(BASE, FN, CTRL)                                   \
-    case BASE + 0: FN<C, CTRL, 0>(v, op, tpred); break;               \
-    case BASE + 1: FN<C, CTRL, 1>(v, op, tpred); break;               \
-    case BASE + 2: FN<C, CTRL, 2>(v, op, tpred); break;               \
-    case BASE + 3: FN<C, CTRL, 3>(v, op, tpred); break;
-    switch (type) {
-        DENSE_CASES(DC_DENSE_REAL_NC, op_dense_real, false)
-        DENSE_CASES(DC_DENSE_CPLX_NC, op_dense, false)
-        case DC_DENSE_CPLX_C + 0: if constexpr (!LEAN) op_dense<C, true, 0>(v, op, tpred); break;
-        case DC_DENSE_CPLX_C + 1: if constexpr (!LEAN) op_dense<C, true, 1>(v, op, tpred); break;
-        case DC_DENSE_CPLX_C + 2: if constexpr (!LEAN) op_dense<C, true, 2>(v, op, tpred); break;
-        case DC_DENSE_CPLX_C + 3: if constexpr (!LEAN) op_dense<C, true, 3>(v, op, tpred); break;
-        case DC_PERMX + 0: if constexpr (!LEAN) op_permx<C, 0>(v, op, tpred); break;
-        case DC_PERMX + 1: if constexpr (!LEAN) op_permx<C, 1>(v, op, tpred); break;
-        case DC_PERMX + 2: if constexpr (!LEAN) op_permx<C, 2>(v, op, tpred); break;
-        case DC_PERMX + 3: if constexpr (!LEAN) op_permx<C, 3>(v, op, tpred); break;
-        case DC_MPHASE: {
-            if constexpr (!LEAN) {
-                const C d = cmake<C, R>((R)op.m(0), (R)op.m(1));
-                const uint32_t rm = op.rmask(), rv = op.rval();
-#pragma unroll
-                for (int j = 0; j < NREG; ++j)
-                    if (((j & rm) == rv) && tpred) v[j] = cmul(v[j], d);
-            }
-            break;
-        }
-        case DC_HADD + 0: op_hadd<C, 0>(v); break;
-        case DC_HADD + 1: op_hadd<C, 1>(v); break;
-        case DC_HADD + 2: op_hadd<C, 2>(v); break;
-        case DC_HADD + 3: op_hadd<C, 3>(v); break;
-#define APPLY_W()                                                              \
-    {                                                                          \
-const double2* w = smT + op.u16_at(0);                                 \
-const uint32_t wm = op.u16_at(2);                                      \
-_Pragma("unroll") for (int j = 0; j < NREG; ++j) if ((wm >> j) & 1) {  \
-    const double2 ww = w[j];                                           \
-    v[j] = cmul(v[j], cmake<C, R>((R)ww.x, (R)ww.y));                  \
-}                                                                      \
-    }
-        case DC_W: APPLY_W() break;
-        case DC_HW + 0: op_hadd<C, 0>(v); APPLY_W() break;
-        case DC_HW + 1: op_hadd<C, 1>(v); APPLY_W() break;
-        case DC_HW + 2: op_hadd<C, 2>(v); APPLY_W() break;
-        case DC_HW + 3: op_hadd<C, 3>(v); APPLY_W() break;
-#undef APPLY_W
-        case DC_TWID: twid_math<C, R>(v, op, smT, smE, tid); break;
-        default:
-            break;
-    }
-#undef DENSE_CASES
-}
+#include "qsv_sweep_ops.cuh"
 
 // gridDim.x re-read at every use: held in a register across a tile it was spilled to local memory
 __device__ __forceinline__ uint32_t grid_x() {
@@ -559,14 +63,6 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 
 // Two instantiations: <256, 1> for 64 KB tiles (k = 12, one CTA per SM) and <128, 3> for smaller tiles
 // (register cap 168 so that three double-buffered 32 KB-tile CTAs share an SM).
-// Three images per (dtype, tile size):
-//   IMG_FULL  every op kind;
-//   IMG_LEAN  the op set of Hadamard/phase circuits only (stage, uncontrolled dense, unnormalised butterfly, phase tables);
-//   IMG_FFT   launches made of OP_FSTAGE ops only: no amplitude is carried in registers from one op to the next, so the
-//             op loop has no register-allocation joins (the generic loop spends ~20 % of its instructions on moves there).
-#define IMG_FULL 0
-#define IMG_LEAN 1
-#define IMG_FFT 2
 template <typename R, int MAXT, int MINB, int IMG>
 __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>::type* __restrict__ src,
                                                   typename cplx_of<R>::type* __restrict__ dst,
@@ -758,30 +254,6 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
 // ================================================================================================
 // host: fusion pass
 // ================================================================================================
-struct PlanStep {
-    bool fused;
-    size_t gate_index;      // !fused: index into ctx->gates
-    SweepParams* params;    // fused (host copy)
-    bool out_of_place;
-    int img;                // kernel image that runs it: IMG_FFT (only OP_FSTAGE ops), IMG_LEAN (lean op set) or IMG_FULL
-    uint64_t n_gates;       // source gates carried
-};
-
-struct SweepPlan {
-    std::vector<PlanStep> steps;
-    std::vector<double> aux;  // host copy of tables
-    double* d_aux = nullptr;
-    int k = 0;
-    uint64_t dropped_identities = 0;
-    std::vector<cudaEvent_t> ev;  // profiling
-    std::vector<float> ms;
-    ~SweepPlan() {
-        for (auto& s : steps) delete s.params;
-        if (d_aux) cudaFree(d_aux);
-        for (auto e : ev) cudaEventDestroy(e);
-    }
-};
-
 void sweep_plan_free(SweepPlan* p) { delete p; }
 
 static SegMap make_segmap(const std::vector<int>& dst_of_src) {
@@ -1757,7 +1229,7 @@ struct Builder {
 static int sweep_set_smem_attr(qsv_ctx* ctx, int k);
 
 // host-only part of the fusion pass: no CUDA call, usable without a device (qsv_hostcheck_fused)
-static int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan) {
+int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan) {
     const int n = ctx->prog_bits;
     if (n < RB) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "unsupported: fused sweeps need at least %d index bits (have %d)", RB, n);
     // default tile: the whole state when it fits, else 2^11 amplitudes (32 KB): measured best on B200 -- three
@@ -2014,207 +1486,4 @@ int sweep_plan_collect_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out) {
     }
     if (n_out) *n_out = n;
     return QSV_OK;
-}
-
-// ================================================================================================
-// Host check of the fusion pass (TEST INFRASTRUCTURE, see include/qsv_hostcheck.h)
-// ================================================================================================
-// Interprets a fused plan on the host, thread by thread, with the SAME op functions the kernel is compiled from
-// (generic_op / fstage_op are __host__ __device__) and the same address tables (swizzled tile slots, per-slot
-// global offsets, per-tile scalars).  It exists so that the planner -- stage selection, phase polynomials,
-// relabelling, budgets, FFT-shape conversion -- can be fuzzed against the oracle on a machine without a GPU.
-// It is not a compute path: nothing in the package calls it, and it refuses states of more than 2^22 amplitudes.
-template <typename R>
-static int sweep_emulate_host(qsv_ctx* ctx, const SweepParams& P, const std::vector<double>& auxv, int img,
-                              const typename cplx_of<R>::type* src, typename cplx_of<R>::type* dst) {
-    typedef typename cplx_of<R>::type C;
-    const SweepDesc& D = P.d;
-    if (D.xg) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "hostcheck: exchange sweeps are not emulated");
-    const int k = D.k;
-    const uint32_t tile_amps = 1u << k;
-    const uint32_t threads = (uint32_t)std::max(32, 1 << (k - RB));  // as sweep_launch
-    const uint32_t n_groups = tile_amps >> RB;
-    const uint64_t n_tiles = 1ull << (D.n_bits - k);
-    const double2* aux2 = reinterpret_cast<const double2*>(auxv.data());
-    const bool dstore = D.direct_store;
-    // (inactive threads of tiny tiles read beyond the tile like the device does beyond its buffer: give them room)
-    std::vector<C> tile_v(std::max<size_t>(tile_amps, 1024));
-    C* tile = tile_v.data();
-    std::vector<double2> smE(MAX_GSLOT), smT(MAX_TAB);
-    for (uint32_t i = 0; i < D.tab_len; ++i) smT[i] = aux2[D.tab_off + i];
-    std::vector<C> regs((size_t)threads * NREG);
-    std::vector<uint32_t> base_l(threads), swbase(threads);
-    for (uint64_t t = 0; t < n_tiles; ++t) {
-        for (uint32_t gs = 0; gs < (uint32_t)D.n_gslots; ++gs) {
-            const double2* gt = aux2 + D.gtab_off + (size_t)gs * D.g_chunks * 16;
-            double2 e = gt[t & 15ull];
-            for (int c = 1; c < D.g_chunks; ++c) e = cmul(e, gt[c * 16 + ((t >> (4 * c)) & 15ull)]);
-            smE[gs] = e;
-        }
-        const uint64_t gin = seg_apply64x(t, D.in_glob), gout = seg_apply64x(t, D.out_glob);
-        auto n_slots_of = [&](uint32_t tid) { return (tid < tile_amps) ? (int)std::max(1u, tile_amps >> D.tb) : 0; };
-        for (uint32_t tid = 0; tid < threads; ++tid) {
-            const uint64_t gb = gin | seg_apply64(tid, D.in_loc);
-            for (int i = 0; i < n_slots_of(tid); ++i) tile[swz(tid) ^ D.ld_soff[i]] = src[gb | D.ld_goff[i]];
-        }
-        auto st_parts = [&](uint32_t tid, uint64_t* t_st_g, uint32_t* t_st_s) {
-            const uint32_t t_st_l = dstore ? expand_rb(tid, D.last_rpos) : seg_apply(tid, D.st_enum);
-            *t_st_g = seg_apply64(t_st_l, D.out_loc);
-            *t_st_s = swz(t_st_l);
-        };
-        bool stored = false, have_stage = false;
-        uint64_t stq[4] = {0, 0, 0, 0};
-        auto roff_of = [&](int j) { return (uint32_t)(stq[j >> 2] >> (16 * (j & 3))) & 0xFFFFu; };
-        for (int i = 0; i < D.n_ops; ++i) {
-            const OpR op = fetch_op(P.ops, i);
-            const uint32_t type = op.type();
-            if (img == IMG_FFT) {
-                if (type < DC_FSTAGE || type >= DC_FIRST_FULL) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: op %d of an FFT launch is not OP_FSTAGE", i);
-                const bool to_hbm = dstore && i == D.n_ops - 1;
-                for (uint32_t tid = 0; tid < threads; ++tid) {
-                    const bool active = tid < n_groups;
-                    uint64_t t_st_g;
-                    uint32_t t_st_s;
-                    st_parts(tid, &t_st_g, &t_st_s);
-                    const uint64_t gbs = gout | t_st_g;
-#define FS(NH, HAS_W) fstage_op<C, R, NH, HAS_W>(op, tile, smT.data(), smE.data(), tid, active, to_hbm, dst, gbs, D.st_goff); break;
-                    switch (type - DC_FSTAGE) {
-                        case 0: case 1: FS(0, false)
-                        case 2: FS(1, false)
-                        case 3: FS(1, true)
-                        case 4: FS(2, false)
-                        case 5: FS(2, true)
-                        case 6: FS(3, false)
-                        case 7: FS(3, true)
-                        case 8: FS(4, false)
-                        default: FS(4, true)
-                    }
-#undef FS
-                }
-                stored = to_hbm;
-                continue;
-            }
-            if (type >= DC_FSTAGE && type < DC_FIRST_FULL) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: OP_FSTAGE in a generic launch");
-            if (img == IMG_LEAN && type >= DC_FIRST_FULL) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: full-image op %u in a lean launch", type);
-            if (type == DC_STAGE) {
-                if (have_stage)
-                    for (uint32_t tid = 0; tid < n_groups && tid < threads; ++tid)
-                        for (int j = 0; j < NREG; ++j) tile[swbase[tid] ^ roff_of(j)] = regs[(size_t)tid * NREG + j];
-                have_stage = true;
-                stq[0] = op.p[0]; stq[1] = op.p[1]; stq[2] = op.p[2]; stq[3] = op.p[3];
-                for (uint32_t tid = 0; tid < threads; ++tid) {
-                    uint32_t b = tid;
-                    for (int q = 0; q < RB; ++q) {
-                        const uint32_t pz = op.rpos(q);
-                        b = ((b >> pz) << (pz + 1)) | (b & ((1u << pz) - 1u));
-                    }
-                    base_l[tid] = b;
-                    swbase[tid] = swz(b);
-                    if (tid < n_groups)
-                        for (int j = 0; j < NREG; ++j) regs[(size_t)tid * NREG + j] = tile[swbase[tid] ^ roff_of(j)];
-                }
-                continue;
-            }
-            if (!have_stage) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: op %d before any stage", i);
-            if (op.gmask && (t & op.gmask) != op.gval) continue;
-            for (uint32_t tid = 0; tid < n_groups && tid < threads; ++tid) {
-                const bool tpred = (base_l[tid] & op.lmask()) == op.lval();
-                C v[NREG];
-                for (int j = 0; j < NREG; ++j) v[j] = regs[(size_t)tid * NREG + j];
-                if (img == IMG_LEAN) generic_op<C, R, true>(v, op, type, tpred, smT.data(), smE.data(), tid);
-                else generic_op<C, R, false>(v, op, type, tpred, smT.data(), smE.data(), tid);
-                for (int j = 0; j < NREG; ++j) regs[(size_t)tid * NREG + j] = v[j];
-            }
-        }
-        if (stored) continue;
-        if (dstore && have_stage) {
-            for (uint32_t tid = 0; tid < n_groups && tid < threads; ++tid) {
-                uint64_t t_st_g;
-                uint32_t t_st_s;
-                st_parts(tid, &t_st_g, &t_st_s);
-                for (int j = 0; j < NREG; ++j) dst[gout | t_st_g | D.st_goff[j]] = regs[(size_t)tid * NREG + j];
-            }
-            continue;
-        }
-        if (have_stage)
-            for (uint32_t tid = 0; tid < n_groups && tid < threads; ++tid)
-                for (int j = 0; j < NREG; ++j) tile[swbase[tid] ^ roff_of(j)] = regs[(size_t)tid * NREG + j];
-        // (in place: every tile reads before it writes and tiles are disjoint, exactly as on the device)
-        for (uint32_t tid = 0; tid < threads; ++tid) {
-            uint64_t t_st_g;
-            uint32_t t_st_s;
-            st_parts(tid, &t_st_g, &t_st_s);
-            for (int i = 0; i < n_slots_of(tid); ++i) dst[gout | t_st_g | D.st_goff[i]] = tile[t_st_s ^ D.st_soff[i]];
-        }
-    }
-    return QSV_OK;
-}
-
-template <typename R>
-static int hostcheck_run(qsv_ctx* ctx, SweepPlan* plan, void* state, uint64_t* out_sweeps, uint64_t* out_fft_sweeps) {
-    typedef typename cplx_of<R>::type C;
-    const size_t amps = (size_t)1 << ctx->prog_bits;
-    std::vector<C> spare_v(amps);
-    C* cur = static_cast<C*>(state);
-    C* other = spare_v.data();
-    uint64_t sweeps = 0, fft = 0;
-    for (auto& st : plan->steps) {
-        if (!st.fused) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "hostcheck: the plan holds a gate that is not fused (dense-k / row pair)");
-        C* d = st.out_of_place ? other : cur;
-        int rc = sweep_emulate_host<R>(ctx, *st.params, plan->aux, st.img, cur, d);
-        if (rc) return rc;
-        if (st.out_of_place) std::swap(cur, other);
-        ++sweeps;
-        fft += st.img == IMG_FFT;
-    }
-    if (cur != static_cast<C*>(state)) memcpy(state, cur, amps * sizeof(C));
-    if (out_sweeps) *out_sweeps = sweeps;
-    if (out_fft_sweeps) *out_fft_sweeps = fft;
-    return QSV_OK;
-}
-
-extern "C" int qsv_hostcheck_fused(int dtype, int n_bits, const qsv_gate_t* gates, uint64_t n_gates, const double* pool, uint64_t pool_elems,
-                                   int max_tile_bits, void* state, uint64_t* out_sweeps, uint64_t* out_fft_sweeps, char* err,
-                                   uint64_t err_len) {
-    qsv_ctx ctx;  // never touches a device
-    ctx.dtype = dtype;
-    int rc = QSV_OK;
-    // state == NULL: plan only (any register the planner accepts) -- the shape of a full-size plan can be asserted on a CPU
-    if ((dtype != QSV_C128 && dtype != QSV_C64) || n_bits < RB || n_bits > (state ? 22 : 40) || (n_gates && !gates)) {
-        rc = qsv_fail(&ctx, QSV_E_INVALID, "hostcheck: bad arguments (n_bits must be %d..22, up to 40 without a state)", RB);
-    } else {
-        for (uint64_t i = 0; i < n_gates && !rc; ++i) {
-            const qsv_gate_t& g = gates[i];
-            if (g.kind > QSV_DIAG1 || g.n_targets != 1 || g.target_bits[0] >= n_bits || (g.ctrl_mask >> n_bits) ||
-                (g.ctrl_mask & (1ull << g.target_bits[0])) || (g.ctrl_value & ~g.ctrl_mask) ||
-                (g.kind != QSV_PERMX && g.matrix_offset + 4 > pool_elems))
-                rc = qsv_fail(&ctx, QSV_E_INVALID, "hostcheck: gate %llu is not a valid one-target gate", (unsigned long long)i);
-        }
-    }
-    SweepPlan* plan = nullptr;
-    if (!rc) {
-        ctx.gates.assign(gates, gates + n_gates);
-        ctx.pool.assign(pool, pool + 2 * pool_elems);
-        ctx.prog_bits = n_bits;
-        ctx.has_program = true;
-        rc = sweep_plan_build_host(&ctx, max_tile_bits, &plan);
-    }
-    if (!rc && !state) {
-        uint64_t sweeps = 0, fft = 0;
-        for (auto& st : plan->steps) {
-            sweeps += st.fused;
-            fft += st.fused && st.img == IMG_FFT;
-        }
-        if (out_sweeps) *out_sweeps = sweeps;
-        if (out_fft_sweeps) *out_fft_sweeps = fft;
-    } else if (!rc) {
-        rc = dtype == QSV_C128 ? hostcheck_run<double>(&ctx, plan, state, out_sweeps, out_fft_sweeps)
-                               : hostcheck_run<float>(&ctx, plan, state, out_sweeps, out_fft_sweeps);
-    }
-    if (plan) sweep_plan_free(plan);
-    if (err && err_len) {
-        strncpy(err, ctx.err, err_len - 1);
-        err[err_len - 1] = 0;
-    }
-    return rc;
 }
