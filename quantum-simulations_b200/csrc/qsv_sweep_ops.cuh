@@ -537,5 +537,6 @@ struct SweepPlan {
 };
 
 
-// host-only part of the fusion pass (qsv_sweep.cu): builds the plan without touching a device
+// the fusion pass (qsv_fuse.cu, host only: builds plans without touching a device)
 int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan);
+int sweep_permute_plan_build(qsv_ctx* ctx, int n_bits, const int* perm, int k, SweepPlan* tmp);
