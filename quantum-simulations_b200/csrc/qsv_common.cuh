@@ -54,8 +54,8 @@ __host__ __device__ __forceinline__ uint64_t bit_expand(uint64_t i, const BitIns
 
 struct Mat2 { double m[8]; };  // row-major (re,im) x 4
 
-// ---- fused-plan types (qsv_sweep.cu) -----------------------------------------------------------
-struct SweepPlan;    // opaque here (qsv_sweep.cu)
+// ---- fused-plan types (qsv_sweep_ops.cuh) -----------------------------------------------------------
+struct SweepPlan;    // opaque here (qsv_sweep_ops.cuh)
 struct RowSlabPlan;  // opaque here (qsv_rows.cu)
 
 struct qsv_ctx {

@@ -1,4 +1,4 @@
-// Shared by qsv_sweep.cu (kernel + fusion pass) and qsv_hostcheck.cu (host interpretation, test infrastructure):
+// Shared by qsv_sweep.cu (kernel), qsv_fuse.cu (fusion pass) and qsv_hostcheck.cu (host interpretation, test infrastructure):
 // launch budgets, the op record and sweep descriptor the kernel reads from parameter space, and the per-op arithmetic,
 // which is __host__ __device__ so that the SAME source runs inside k_sweep and inside the host check.
 #pragma once
