@@ -220,3 +220,47 @@ def test_apply_stream_bookkeeping_with_a_host_engine(refuse):
     assert len(eng.calls) == -(-len(gates) // 16) and (all(eng.calls) if not refuse else not all(eng.calls))
     one = apply_stream(gates, x[:, 0], reg, chunk_gates=1 << 18, engine=_HostEngine())
     assert one.shape == (1 << n,) and np.abs(one - want[:, 0]).max() < 1e-12
+
+
+def _naive_records(gates, reg, batch_bits):
+    """Per-gate restatement of the record conventions (program.py header), independent of RecordWriter."""
+    from quantum_simulations_b200._lib import GATE_DTYPE
+    n = len(reg)
+    pos = {q: i for i, q in enumerate(reg)}
+    recs, pool = [], []
+    for g in gates:
+        r = np.zeros((), dtype=GATE_DTYPE)
+        mask = value = 0
+        tb = []
+        for q, c in zip(g.qspace, g.controls()):
+            bit = n - 1 - pos[q] + batch_bits
+            if int(c) == 4:
+                mask |= 1 << bit
+                value |= 1 << bit
+            elif int(c) == 2:
+                mask |= 1 << bit
+            else:
+                tb.append(bit)
+        m = np.asarray(g.matrix(), dtype=np.complex128) * complex(g.phase())
+        r["n_targets"], r["ctrl_mask"], r["ctrl_value"] = len(tb), mask, value
+        r["target_bits"][:len(tb)] = tb
+        if len(tb) == 1 and np.array_equal(m, [[0, 1], [1, 0]]):
+            r["kind"] = 1
+        else:
+            r["kind"] = 3 if len(tb) > 1 else (2 if (m[0, 1] == 0 and m[1, 0] == 0) else 0)
+            r["matrix_offset"] = sum(p.size for p in pool)
+            pool.append(m.reshape(-1))
+        recs.append(r)
+    return np.array(recs, dtype=GATE_DTYPE), (np.concatenate(pool) if pool else np.zeros(0, complex))
+
+
+@pytest.mark.parametrize("batch_bits", [0, 4])
+def test_program_records_against_a_naive_flattener(batch_bits):
+    n = 7
+    gates = _random_gates(n, 250, 33)
+    reg = [qs.Qubit(i) for i in range(n)]
+    want, wpool = _naive_records(gates, reg, batch_bits)
+    prog = flatten(gates, reg)
+    assert prog.records(batch_bits).tobytes() == want.tobytes()
+    assert np.array_equal(prog.pool(), wpool)
+    assert prog.records(batch_bits).tobytes() == want.tobytes()      # records() does not consume the program
