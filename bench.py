@@ -321,9 +321,10 @@ def run_single(args):
             "data": "synthetic",
             "config": {"workload": f"qft{n}_statevector_c128", "qubits": n, "amplitudes": amps, "gates": n_gates, "fused": fused,
                        "sweeps_per_step": n_sweeps, "l2": "state (16 B x 2^n) is far larger than the 126 MB L2"},
-            "amp_GBps": amp_gbps, "hbm_frac_of_measured": amp_gbps / peak,
+            "amp_GBps": amp_gbps, "hbm_frac_of_measured": amp_gbps / peak, "hbm_frac_of_nominal_8TBps": amp_gbps / 8000.0,
             "roofline": {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                         "frac": achieved / peak, "bytes_per_launch": per_launch_bytes, "avg_launch_ms": avg_ms,
+                         "frac": achieved / peak, "frac_of_nominal_8TBps": achieved / 8000.0, "bytes_per_launch": per_launch_bytes,
+                         "avg_launch_ms": avg_ms,
                          "traffic": ncu_traffic(n) if fused else None},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "sweep_ms_first_step": sweep_ms}
     print(json.dumps(line))
