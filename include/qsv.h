@@ -153,6 +153,15 @@ int qsv_init_basis_columns(qsv_ctx* ctx, void* state, int n_bits, int batch_bits
  * trace / qproject with |0> (cgate.py:228-305, inter_product.py:318-363).           */
 int qsv_project_ancilla(qsv_ctx* ctx, const void* in, void* out, int n_bits, int batch_bits,
                         uint64_t ancilla_mask, void* stream);
+/* The same two steps with every ancilla in the single-qubit pure state psi = (psi[0] + i psi[1]) |0> +
+ * (psi[2] + i psi[3]) |1> instead of |0>: column j starts as |e(col0 + j)> (x) psi (x) ... (x) psi, and the read-out
+ * contracts every ancilla with <psi|: out[r] = sum_v conj(prod_i psi_{v_i}) in[r, ancillas = v].  Together they are
+ * the sandwich <psi| U |psi> of CtrlGate.dela(state) / trace(qubit, state) for a state other than |0>
+ * (cgate.py:228-305; qproject, inter_product.py:357-363).  At most 16 ancillas.          */
+int qsv_init_basis_columns_psi(qsv_ctx* ctx, void* state, int n_bits, int batch_bits, uint64_t col0,
+                               uint64_t ancilla_mask, const double psi[4], void* stream);
+int qsv_project_ancilla_psi(qsv_ctx* ctx, const void* in, void* out, int n_bits, int batch_bits,
+                            uint64_t ancilla_mask, const double psi[4], void* stream);
 /* out[y] = in[x] where bit perm[i] of y equals bit i of x.  Replaces
  * Permuter.bitsortall + np.ix_ in CtrlGate.sorted (cgate.py:181-183,
  * quompiler/utils/permute.py:60-121); also the local half of a qubit remap.         */

@@ -18,6 +18,8 @@ def load():
         _lib = C.CDLL(_PATH)
         _lib.orc_run.restype = C.c_int
         _lib.orc_run.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]
+        _lib.orc_set_threads.argtypes = [C.c_int]
+        _lib.orc_get_threads.restype = C.c_int
     return _lib
 
 
@@ -33,5 +35,18 @@ def run_records(recs, pool, state, n_bits, batch_bits=0):
     return state
 
 
+def set_threads(n: int = 0) -> int:
+    """Use ``n`` OpenMP threads (0 = every core this process may run on), whatever OMP_NUM_THREADS says --
+    torch.distributed.run exports OMP_NUM_THREADS=1 to its workers.  Returns the count in effect."""
+    if n <= 0:
+        try:
+            n = len(os.sched_getaffinity(0))
+        except AttributeError:
+            n = os.cpu_count() or 1
+    load().orc_set_threads(int(n))
+    return threads()
+
+
 def threads() -> int:
-    return int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))
+    """The thread count the OpenMP loops will really use."""
+    return int(load().orc_get_threads())

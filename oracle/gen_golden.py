@@ -364,10 +364,99 @@ def gen_optimizer():
     np.savez_compressed(os.path.join(OUT, "optimizer.npz"), **out)
 
 
+def gen_trace():
+    """CtrlGate.trace(qubit, state) / dela(state) with states other than |0> (cgate.py:228-305, qproject
+    inter_product.py:318-363; cases shaped like test_cgate.py:673-806).
+
+    (a) single gates: every (gate, qubit, state) is recorded with the reference's outcome -- the traced gate, or the
+        fact that the reference raised (its constructor rejects a non-unitary result);
+    (b) products with ancillas: the sandwich <psi|V|psi> on every ancilla of V = reduce(@), taken with the reference's
+        own qproject on V.sorted().inflate() (valid for any state), and V.dela(psi).inflate() where the reference
+        accepts it."""
+    from quompiler.utils.inter_product import qproject, mykron
+    seed()
+    out = {}
+    states = [np.array([1, 0]), np.array([0, 1]), np.array([1, 1]) / np.sqrt(2), random_state(2), random_state(2)]
+    src, res, which, st_used, ok = [], [], [], [], []
+    cases = []
+    for ctrl in (QType.CONTROL0, QType.CONTROL1):
+        for qidx in (0, 1):
+            u = random_unitary(2)
+            mat = np.kron(np.eye(2), u) if qidx == 0 else np.kron(u, np.eye(2))
+            cases.append(CtrlGate(mat, [ctrl, QType.TARGET, QType.TARGET]))
+        cases.append(CtrlGate(random_unitary(2), [ctrl, QType.TARGET], phase=np.exp(0.7j)))
+        cases.append(CtrlGate(random_unitary(4), [QType.TARGET, ctrl, QType.TARGET], [Qubit(4), Qubit(2), Qubit(9, ancilla=True)]))
+    cases.append(CtrlGate(mykron(np.eye(2), random_unitary(2), np.eye(2)), [QType.CONTROL1] + [QType.TARGET] * 3,
+                          [Qubit(10), Qubit(12, ancilla=True), Qubit(7), Qubit(1, ancilla=True)]))
+    for g in cases:
+        for qi, q in enumerate(g.qspace):
+            for si, st in enumerate(states):
+                try:
+                    r = g.trace(q, st)
+                    good = True
+                except (AssertionError, NotImplementedError):
+                    r = CtrlGate(np.eye(2), [QType.TARGET])
+                    good = False
+                src.append(g)
+                res.append(r)
+                which.append(qi)
+                st_used.append(st.astype(np.complex128))
+                ok.append(good)
+    out.update(prefixed("src", pack_gates(src)))
+    out.update(prefixed("res", pack_gates(res)))
+    out["which"] = np.array(which)
+    out["state"] = np.array(st_used)
+    out["ok"] = np.array(ok)
+    # (b) products
+    chains, vals, cstate, ref_ok, ref_vals = [], [], [], [], []
+    a1, a2 = Qubit(101, ancilla=True), Qubit(102, ancilla=True)
+    T, C0, C1 = QType.TARGET, QType.CONTROL0, QType.CONTROL1
+    for trial in range(10):
+        qs_ = [Qubit(0), Qubit(1), Qubit(2)]
+        anc = [a1] if trial % 2 == 0 else [a1, a2]
+        gates = []
+        for _ in range(4):
+            pick = random.sample(qs_ + anc, 3)
+            gates.append(CtrlGate(random_unitary(2), random_control(3, 1), pick))
+        if trial >= 6:   # ancillas only ever used as controls: with a basis state the reference accepts the result
+            gates = [CtrlGate(random_unitary(2), [random.choice([C0, C1]), T], [anc[0], random.choice(qs_)]) for _ in range(3)]
+            gates.append(CtrlGate(random_unitary(2), [T, C1], [qs_[0], qs_[1]]))
+        st = states[trial % len(states)] if trial < 6 else states[trial % 2]
+        V = reduce(lambda a, b: a @ b, gates).sorted()
+        m = V.inflate()
+        space = list(V.qspace)
+        for q in [q for q in space if q.ancilla][::-1]:
+            m = qproject(m, space.index(q), st)
+            space.remove(q)
+        try:
+            rv = V.dela(st).inflate()
+            r_ok = True
+        except AssertionError:
+            rv = np.zeros_like(m)
+            r_ok = False
+        chains.append(gates)
+        vals.append(m)
+        cstate.append(st.astype(np.complex128))
+        ref_ok.append(r_ok)
+        ref_vals.append(rv)
+    for i, gates in enumerate(chains):
+        out.update(prefixed(f"chain{i}", pack_gates(gates)))
+        out[f"chain{i}_value"] = vals[i]
+        out[f"chain{i}_refdela"] = ref_vals[i]
+    out["chain_state"] = np.array(cstate)
+    out["chain_ref_ok"] = np.array(ref_ok)
+    out["n_chains"] = np.array(len(chains))
+    np.savez_compressed(os.path.join(OUT, "trace.npz"), **out)
+    print("trace", len(src), "single cases,", int(np.sum(ok)), "accepted;", len(chains), "chains,", int(np.sum(ref_ok)), "accepted by the reference")
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     if len(sys.argv) > 1 and sys.argv[1] == "optimizer":
         gen_optimizer()
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "trace":
+        gen_trace()
         sys.exit(0)
     gen_single_gates()
     gen_transforms()
@@ -377,4 +466,5 @@ if __name__ == "__main__":
     gen_two_level()
     gen_qco()
     gen_optimizer()
+    gen_trace()
     print("done ->", os.path.abspath(OUT))

@@ -9,6 +9,7 @@
  * (test_c_oracle_matches_numpy_oracle).
  */
 #include <complex.h>
+#include <omp.h>
 #include <stdint.h>
 #include <string.h>
 
@@ -79,6 +80,13 @@ static void applyk(cd* st, int n_bits, const qsv_gate_t* g, const cd* m) {
         for (int v = 0; v < D; ++v) st[x | off[v]] = out[v];
     }
 }
+
+/* Thread count of the parallel loops.  torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the timed CPU
+ * baseline must not inherit that by accident, so bench.py sets the count explicitly and reports what it got. */
+void orc_set_threads(int n) {
+    if (n > 0) omp_set_num_threads(n);
+}
+int orc_get_threads(void) { return omp_get_max_threads(); }
 
 /* Applies `n_gates` records (time order) to a complex128 state of 2^n_bits amplitudes. */
 int orc_run(double* state, int n_bits, int batch_bits, const qsv_gate_t* gates, uint64_t n_gates, const double* pool) {

@@ -43,7 +43,7 @@ class B200Circuit:
         Ancillas are kept as ordinary qubits unless ``drop_ancilla``; with it the result
         is <0|U|0> on the ancillas, i.e. the reference's ``.dela().inflate()``.
         """
-        from ..engine import get_engine, simulate_columns
+        from ..engine import _try_fuse, get_engine, simulate_columns
         import torch
         prog = self.program(qubit_order)
         if drop_ancilla:
@@ -55,13 +55,9 @@ class B200Circuit:
         eng.init_basis_columns(state, 2 * n, n, 0, 0)
         eng.upload(prog, n)
         spare = None
-        if fuse:
-            try:
-                eng.fuse()
-                spare = eng.empty(1 << (2 * n))
-            except Exception as e:
-                if "not built" not in str(e) and "unsupported" not in str(e).lower():
-                    raise
+        self.fused = bool(fuse and _try_fuse(eng))     # False = ran one kernel per gate (a RuntimeWarning said why)
+        if self.fused:
+            spare = eng.empty(1 << (2 * n))
         res = eng.run(state, spare)
         torch.cuda.synchronize(eng.device)
         return res.view(1 << n, 1 << n).cpu().numpy()

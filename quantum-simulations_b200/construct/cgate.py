@@ -17,6 +17,18 @@ from .su2gate import RGate
 from .types import CONTROL0, CONTROL1, TARGET, IDLER, QType, UnivGate, proportional
 
 
+def project_factor(core: np.ndarray, idx: int, state) -> np.ndarray:
+    """``<state| core |state>`` on tensor factor ``idx`` (0 = most significant) of a ``2^t x 2^t`` matrix: the
+    reference's ``qproject`` (``utils/inter_product.py:318-363``) as one tensor contraction."""
+    t = core.shape[0].bit_length() - 1
+    assert core.shape == (1 << t, 1 << t) and t >= 2 and 0 <= idx < t
+    s = np.asarray(state, dtype=np.complex128)
+    ten = np.asarray(core, dtype=np.complex128).reshape((2,) * (2 * t))
+    ten = np.tensordot(np.conj(s), ten, axes=([0], [idx]))            # row factor gone: axes shift down by one
+    ten = np.tensordot(ten, s, axes=([t - 1 + idx], [0]))
+    return ten.reshape(1 << (t - 1), 1 << (t - 1))
+
+
 def _is_rgate(g) -> bool:
     return isinstance(g, RGate) or (type(g).__name__ == 'RGate' and hasattr(g, 'angle') and hasattr(g, 'axis'))
 
@@ -241,8 +253,35 @@ class CtrlGate:
         from .chain import GateChain
         return GateChain([self]).dela(state)
 
-    def trace(self, qubit, state):
-        raise NotImplementedError('single-qubit projection with an arbitrary state is not on the simulation path; use dela() (|0> on every ancilla)')
+    def trace(self, qubit, state) -> 'CtrlGate':
+        """Fix one qubit of the gate in the pure state ``state`` and return the gate left on the others
+        (``cgate.py:228-287``).  Work on the gate's own ``2^t x 2^t`` core only:
+
+        * control qubit: the controlled block acts with weight ``|<active|state>|^2``, the identity with the rest;
+        * target qubit: ``<state| core |state>`` on that tensor factor (``qproject``, ``inter_product.py:318-363``);
+          a gate whose only target is traced leaves the identity, as in the reference.
+
+        Like the reference, the result goes through the constructor, which rejects a non-unitary outcome.
+        """
+        assert qubit in self._qontrol, f'Qubit {qubit} not in qspace.'
+        state = np.asarray(state)
+        assert state.shape == (2,), f'state vector must be a 1D array of length 2, but got {state.shape}.'
+        assert np.isclose(np.linalg.norm(state), 1), f'state vector must normalized but got {state}.'
+        role = int(self._qontrol[qubit])
+        if role == IDLER:
+            raise NotImplementedError(f"CtrlGate {self._qontrol[qubit]} not implemented.")
+        rest = [q for q in self.qspace if q != qubit]
+        roles = [self._qontrol[q] for q in rest]
+        if role in (CONTROL0, CONTROL1):
+            w_idle, w_act = abs(state[0]) ** 2, abs(state[1]) ** 2
+            if role == CONTROL0:
+                w_idle, w_act = w_act, w_idle
+            core = w_idle * np.eye(self._matrix.shape[0]) + w_act * self._matrix
+            return CtrlGate(core, roles, rest, self._phase)
+        targets = self.target_qids()
+        if len(targets) == 1:
+            return CtrlGate(UnivGate.I, [QType.TARGET], rest, self._phase)
+        return CtrlGate(project_factor(self._matrix, targets.index(qubit), state), roles, rest, self._phase)
 
     def is_idler(self, qubit) -> bool:
         return qubit not in self._qontrol

@@ -16,10 +16,11 @@ from .qspace import qubit_key
 
 
 class GateChain:
-    def __init__(self, gates, register=None, drop_ancilla=False):
+    def __init__(self, gates, register=None, drop_ancilla=False, ancilla_state=None):
         self.gates = list(gates)          # matrix-product order: gates[0] is the left-most factor
         self._register = list(register) if register is not None else None
         self._drop = drop_ancilla
+        self._anc_state = ancilla_state   # None = |0>
         kinds = {hasattr(g, 'qspace') for g in self.gates}
         assert len(kinds) == 1, 'cannot mix UnitaryM and CtrlGate in one product'
         self._qubit_gates = kinds.pop()
@@ -66,18 +67,24 @@ class GateChain:
     def sorted(self, sorting=None):
         if sorting is not None:
             raise NotImplementedError('a lazy product is always reported over the sorted register')
-        return GateChain(self.gates, None, self._drop)
+        return GateChain(self.gates, None, self._drop, self._anc_state)
 
     def dela(self, state=None):
-        if state is not None and not np.allclose(np.asarray(state), [1, 0]):
-            raise NotImplementedError('only projection on |0> is implemented on the device')
-        return GateChain(self.gates, self._register, True)
+        """Ancillas fixed in ``state`` (default |0>) on both sides: the sandwich ``<state| U |state>`` of
+        ``cgate.py:289-305`` taken on the product's dense operator, evaluated on the device (ancilla bits of the
+        basis columns start in ``state``, the read-out contracts them with ``<state|``).  Unlike the reference, a
+        non-unitary outcome is returned rather than rejected: the lazy product never builds a ``CtrlGate``."""
+        if state is not None:
+            assert isinstance(state, np.ndarray), 'state vector must be a np.ndarray.'
+            assert state.shape == (2,), f'state vector must be a 1D array of length 2, but got {state.shape}'
+        return GateChain(self.gates, self._register, True, state)
 
     # -- evaluation ----------------------------------------------------------------------
     def inflate(self, dtype=np.complex128) -> np.ndarray:
         from ..engine import reconstruct_unitary, reconstruct_unitary_rows
         if self._qubit_gates:
-            return reconstruct_unitary(self.gates[::-1], self._full_register(), drop_ancilla=self._drop, dtype=dtype)
+            return reconstruct_unitary(self.gates[::-1], self._full_register(), drop_ancilla=self._drop, dtype=dtype,
+                                       ancilla_state=self._anc_state if self._drop else None)
         return reconstruct_unitary_rows(self.gates[::-1], self.dimension, dtype=dtype)
 
     def __array__(self, dtype=None, copy=None):

@@ -15,6 +15,9 @@
 #include <stdarg.h>
 #include <stdlib.h>
 
+#include <algorithm>
+#include <cmath>
+
 #include "qsv_common.cuh"
 
 static char g_create_err[512] = {0};
@@ -212,6 +215,51 @@ __global__ void __launch_bounds__(256) k_project(const typename cplx_of<R>::type
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nout; i += stride)
         out[i] = in[bit_expand(i, anc)];
+}
+
+// Ancillas in a pure state psi instead of |0>: thread (j, v) writes column j's amplitude for ancilla assignment v
+struct Psi { double a_re, a_im, b_re, b_im; };
+
+template <typename R>
+__global__ void k_basis_psi(typename cplx_of<R>::type* __restrict__ st, uint64_t ncols, int batch_bits, uint64_t col0,
+                            BitInsert anc, Psi psi) {
+    typedef typename cplx_of<R>::type C;
+    const uint64_t id = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t j = id % ncols, v = id / ncols;
+    if (v >> anc.n) return;
+    uint64_t row = bit_expand(col0 + j, anc);
+    double2 w = make_double2(1.0, 0.0);
+    for (int i = 0; i < anc.n; ++i) {
+        const bool one = (v >> i) & 1ull;
+        if (one) row |= 1ull << anc.pos[i];
+        w = cmul(w, one ? make_double2(psi.b_re, psi.b_im) : make_double2(psi.a_re, psi.a_im));
+    }
+    st[(row << batch_bits) | j] = cmake<C, R>((R)w.x, (R)w.y);
+}
+
+// out[i] = sum_v conj(prod_i psi_{v_i}) in[expand(i) | ancillas = v]   (<psi| on every ancilla)
+template <typename R>
+__global__ void __launch_bounds__(256) k_project_psi(const typename cplx_of<R>::type* __restrict__ in,
+                                                     typename cplx_of<R>::type* __restrict__ out, uint64_t nout,
+                                                     BitInsert anc, Psi psi) {
+    typedef typename cplx_of<R>::type C;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nout; i += stride) {
+        const uint64_t base = bit_expand(i, anc);
+        double2 acc = make_double2(0.0, 0.0);
+        for (uint64_t v = 0; !(v >> anc.n); ++v) {
+            uint64_t x = base;
+            double2 w = make_double2(1.0, 0.0);
+            for (int q = 0; q < anc.n; ++q) {
+                const bool one = (v >> q) & 1ull;
+                if (one) x |= 1ull << anc.pos[q];
+                w = cmul(w, one ? make_double2(psi.b_re, -psi.b_im) : make_double2(psi.a_re, -psi.a_im));
+            }
+            const C a = in[x];
+            acc = cfma(w, make_double2((double)a.x, (double)a.y), acc);
+        }
+        out[i] = cmake<C, R>((R)acc.x, (R)acc.y);
+    }
 }
 
 struct BitPerm { int n; uint8_t to[64]; };
@@ -622,14 +670,29 @@ int qsv_upload_program(qsv_ctx* ctx, int n_bits, int batch_bits, const qsv_gate_
     for (uint64_t i = 0; i < n_gates; ++i) {
         const qsv_gate_t& g = gates[i];
         if (g.kind > QSV_ROWS2) return qsv_fail(ctx, QSV_E_INVALID, "gate %llu: unknown kind %u", (unsigned long long)i, g.kind);
+        if (g.kind != QSV_ROWS2 && (g.n_targets < 1 || g.n_targets > QSV_MAX_TARGETS))  // (before the shift below uses it)
+            return qsv_fail(ctx, QSV_E_UNSUPPORTED, "gate %llu: %u targets (max %d)", (unsigned long long)i, g.n_targets, QSV_MAX_TARGETS);
         uint64_t need = 0;
         if (g.kind == QSV_ROWS2) need = 4;
         else if (g.kind != QSV_PERMX) need = 1ull << (2 * g.n_targets);
-        if (need && g.matrix_offset + need > pool_elems)
+        if (need && (g.matrix_offset > pool_elems || need > pool_elems - g.matrix_offset))
             return qsv_fail(ctx, QSV_E_INVALID, "gate %llu: matrix outside the pool", (unsigned long long)i);
+        if (need && !pool) return qsv_fail(ctx, QSV_E_INVALID, "pool is NULL");
+        if (g.kind == QSV_ROWS2) {
+            const uint64_t dim = 1ull << (n_bits - batch_bits);
+            if (g.row0 >= dim || g.row1 >= dim || g.row0 == g.row1)
+                return qsv_fail(ctx, QSV_E_INVALID, "gate %llu: rows (%llu, %llu) must be distinct and below %llu", (unsigned long long)i,
+                                (unsigned long long)g.row0, (unsigned long long)g.row1, (unsigned long long)dim);
+        }
+        if (g.kind == QSV_DIAG1) {
+            // the fused path folds diagonals into a phase polynomial (angles only): a non-unit modulus would be applied by the
+            // per-gate kernels and dropped by the fused ones, so it is refused here for both
+            const double* m = pool + 2 * g.matrix_offset;
+            const double r0 = m[0] * m[0] + m[1] * m[1], r1 = m[6] * m[6] + m[7] * m[7];
+            if (!(std::fabs(r0 - 1.0) <= 1e-6) || !(std::fabs(r1 - 1.0) <= 1e-6) || m[2] != 0 || m[3] != 0 || m[4] != 0 || m[5] != 0)
+                return qsv_fail(ctx, QSV_E_INVALID, "gate %llu: a diagonal record needs unit-modulus entries and a zero off-diagonal", (unsigned long long)i);
+        }
         if (g.kind != QSV_ROWS2) {
-            if (g.n_targets < 1 || g.n_targets > QSV_MAX_TARGETS)
-                return qsv_fail(ctx, QSV_E_UNSUPPORTED, "gate %llu: %u targets (max %d)", (unsigned long long)i, g.n_targets, QSV_MAX_TARGETS);
             BitInsert ins;
             int rc = build_insert(ctx, &g, n_bits, &ins, true);
             if (rc) return rc;
@@ -755,6 +818,69 @@ int qsv_project_ancilla(qsv_ctx* ctx, const void* in, void* out, int n_bits, int
         k_project<double><<<blocks, 256, 0, s>>>((const double2*)in, (double2*)out, nout, anc);
     else
         k_project<float><<<blocks, 256, 0, s>>>((const float2*)in, (float2*)out, nout, anc);
+    ctx->stats.kernel_launches++;
+    QSV_CUDA(ctx, cudaGetLastError());
+    return QSV_OK;
+}
+
+static int psi_args(qsv_ctx* ctx, int n_bits, int batch_bits, uint64_t ancilla_mask, const double* psi, int shift, BitInsert* anc, Psi* p) {
+    if (n_bits < 1 || n_bits > 62 || batch_bits < 0 || batch_bits > n_bits) return qsv_fail(ctx, QSV_E_INVALID, "bad sizes");
+    const int row_bits = n_bits - batch_bits;
+    if (row_bits < 64 && (ancilla_mask >> row_bits)) return qsv_fail(ctx, QSV_E_INVALID, "ancilla mask exceeds the row bits");
+    if (!psi) return qsv_fail(ctx, QSV_E_INVALID, "psi is NULL");
+    const double nrm = psi[0] * psi[0] + psi[1] * psi[1] + psi[2] * psi[2] + psi[3] * psi[3];
+    if (!(std::fabs(nrm - 1.0) <= 1e-8)) return qsv_fail(ctx, QSV_E_INVALID, "psi is not normalised (|psi|^2 = %g)", nrm);
+    if (__builtin_popcountll(ancilla_mask) > 16) return qsv_fail(ctx, QSV_E_TOOBIG, "more than 16 ancillas in a general state");
+    anc->n = 0;
+    anc->value = 0;
+    for (int b = 0; b < row_bits; ++b)
+        if (ancilla_mask & (1ull << b)) anc->pos[anc->n++] = (uint8_t)(b + shift);
+    p->a_re = psi[0]; p->a_im = psi[1]; p->b_re = psi[2]; p->b_im = psi[3];
+    return QSV_OK;
+}
+
+int qsv_init_basis_columns_psi(qsv_ctx* ctx, void* state, int n_bits, int batch_bits, uint64_t col0, uint64_t ancilla_mask,
+                               const double psi[4], void* stream) {
+    if (!ctx) return QSV_E_INVALID;
+    if (!state) return qsv_fail(ctx, QSV_E_INVALID, "state is NULL");
+    BitInsert anc;
+    Psi p;
+    int rc = psi_args(ctx, n_bits, batch_bits, ancilla_mask, psi, 0, &anc, &p);
+    if (rc) return rc;
+    const int free_bits = n_bits - batch_bits - anc.n;
+    const uint64_t ncols = 1ull << batch_bits;
+    if (col0 + ncols > (1ull << free_bits)) return qsv_fail(ctx, QSV_E_INVALID, "columns [%llu,%llu) exceed 2^%d basis states",
+                                                            (unsigned long long)col0, (unsigned long long)(col0 + ncols), free_bits);
+    cudaStream_t s = (cudaStream_t)stream;
+    QSV_CUDA(ctx, cudaSetDevice(ctx->device));
+    QSV_CUDA(ctx, cudaMemsetAsync(state, 0, amp_size(ctx->dtype) << n_bits, s));
+    const uint64_t work = ncols << anc.n;
+    const unsigned blocks = (unsigned)((work + 255) / 256);
+    if (ctx->dtype == QSV_C128)
+        k_basis_psi<double><<<blocks, 256, 0, s>>>((double2*)state, ncols, batch_bits, col0, anc, p);
+    else
+        k_basis_psi<float><<<blocks, 256, 0, s>>>((float2*)state, ncols, batch_bits, col0, anc, p);
+    ctx->stats.kernel_launches++;
+    QSV_CUDA(ctx, cudaGetLastError());
+    return QSV_OK;
+}
+
+int qsv_project_ancilla_psi(qsv_ctx* ctx, const void* in, void* out, int n_bits, int batch_bits, uint64_t ancilla_mask,
+                            const double psi[4], void* stream) {
+    if (!ctx) return QSV_E_INVALID;
+    if (!in || !out) return qsv_fail(ctx, QSV_E_INVALID, "NULL buffer");
+    BitInsert anc;
+    Psi p;
+    int rc = psi_args(ctx, n_bits, batch_bits, ancilla_mask, psi, batch_bits, &anc, &p);
+    if (rc) return rc;
+    const uint64_t nout = 1ull << (n_bits - anc.n);
+    cudaStream_t s = (cudaStream_t)stream;
+    QSV_CUDA(ctx, cudaSetDevice(ctx->device));
+    const unsigned blocks = (unsigned)std::min<uint64_t>((nout + 255) / 256, 148 * 16);
+    if (ctx->dtype == QSV_C128)
+        k_project_psi<double><<<blocks, 256, 0, s>>>((const double2*)in, (double2*)out, nout, anc, p);
+    else
+        k_project_psi<float><<<blocks, 256, 0, s>>>((const float2*)in, (float2*)out, nout, anc, p);
     ctx->stats.kernel_launches++;
     QSV_CUDA(ctx, cudaGetLastError());
     return QSV_OK;

@@ -64,8 +64,9 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // Two instantiations: <256, 1> for 64 KB tiles (k = 12, one CTA per SM) and <128, 3> for smaller tiles
 // (register cap 168 so that three double-buffered 32 KB-tile CTAs share an SM).
 template <typename R, int MAXT, int MINB, int IMG>
-__global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>::type* __restrict__ src,
-                                                  typename cplx_of<R>::type* __restrict__ dst,
+// (src and dst are NOT __restrict__: every in-place sweep is launched with dst == src)
+__global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>::type* src,
+                                                  typename cplx_of<R>::type* dst,
                                                   const double* __restrict__ aux,
                                                   const __grid_constant__ SweepParams P) {
     typedef typename cplx_of<R>::type C;

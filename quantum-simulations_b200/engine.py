@@ -141,15 +141,36 @@ class Engine:
         check(self.lib.qsv_apply_rows(self._ctx, C.c_void_p(state.data_ptr()), dim, batch, rows.ctypes.data_as(C.c_void_p),
                                       len(rows), m.ctypes.data_as(C.c_void_p), self._stream()), self._ctx)
 
-    def init_basis_columns(self, state, n_bits: int, batch_bits: int, col0: int = 0, ancilla_mask: int = 0):
-        check(self.lib.qsv_init_basis_columns(self._ctx, C.c_void_p(state.data_ptr()), n_bits, batch_bits, col0, ancilla_mask,
-                                              self._stream()), self._ctx)
+    @staticmethod
+    def _psi(ancilla_state):
+        """None (= |0>) or the four doubles (re a, im a, re b, im b) of a|0> + b|1>."""
+        if ancilla_state is None:
+            return None
+        st = np.asarray(ancilla_state, dtype=np.complex128)
+        assert st.shape == (2,), f'state vector must be a 1D array of length 2, but got {st.shape}'
+        if st[0] == 1 and st[1] == 0:
+            return None
+        return (C.c_double * 4)(st[0].real, st[0].imag, st[1].real, st[1].imag)
 
-    def project_ancilla(self, src, n_bits: int, batch_bits: int, ancilla_mask: int):
+    def init_basis_columns(self, state, n_bits: int, batch_bits: int, col0: int = 0, ancilla_mask: int = 0, ancilla_state=None):
+        psi = self._psi(ancilla_state)
+        if psi is None or not ancilla_mask:
+            check(self.lib.qsv_init_basis_columns(self._ctx, C.c_void_p(state.data_ptr()), n_bits, batch_bits, col0, ancilla_mask,
+                                                  self._stream()), self._ctx)
+        else:
+            check(self.lib.qsv_init_basis_columns_psi(self._ctx, C.c_void_p(state.data_ptr()), n_bits, batch_bits, col0,
+                                                      ancilla_mask, psi, self._stream()), self._ctx)
+
+    def project_ancilla(self, src, n_bits: int, batch_bits: int, ancilla_mask: int, ancilla_state=None):
         n_out = (1 << n_bits) >> bin(ancilla_mask).count("1")
         out = self.empty(n_out)
-        check(self.lib.qsv_project_ancilla(self._ctx, C.c_void_p(src.data_ptr()), C.c_void_p(out.data_ptr()), n_bits, batch_bits,
-                                           ancilla_mask, self._stream()), self._ctx)
+        psi = self._psi(ancilla_state)
+        if psi is None:
+            check(self.lib.qsv_project_ancilla(self._ctx, C.c_void_p(src.data_ptr()), C.c_void_p(out.data_ptr()), n_bits,
+                                               batch_bits, ancilla_mask, self._stream()), self._ctx)
+        else:
+            check(self.lib.qsv_project_ancilla_psi(self._ctx, C.c_void_p(src.data_ptr()), C.c_void_p(out.data_ptr()), n_bits,
+                                                   batch_bits, ancilla_mask, psi, self._stream()), self._ctx)
         return out
 
     def permute_bits(self, src, n_bits: int, perm):
@@ -182,6 +203,25 @@ class Engine:
 
 
 _ENGINES = {}
+_WARNED = set()
+
+
+def _try_fuse(eng) -> bool:
+    """Build the fused plan; when the fusion pass refuses the program ("unsupported": e.g. fewer index bits than a
+    register stage) the program still runs on the GPU, one kernel per gate -- many times slower on long streams, so
+    say so once per reason instead of downgrading silently.  Any other error propagates."""
+    import warnings
+    try:
+        eng.fuse()
+        return True
+    except QsvError as e:
+        msg = str(e)
+        if "unsupported" not in msg.lower():
+            raise
+        if msg not in _WARNED:
+            _WARNED.add(msg)
+            warnings.warn(f"fused sweeps unavailable for this program, running one kernel per gate: {msg}", RuntimeWarning, stacklevel=3)
+        return False
 
 
 def get_engine(dtype=np.complex128, device=None) -> Engine:
@@ -198,8 +238,9 @@ def _pow2_ceil_bits(n: int) -> int:
 
 
 def simulate_columns(program: Program, col0: int, n_cols_bits: int, dtype=np.complex128, fuse=True, engine=None,
-                     drop_ancilla=True, return_device=False):
-    """Run ``program`` on the basis columns ``col0 .. col0 + 2^n_cols_bits`` (ancillas in |0>).
+                     drop_ancilla=True, return_device=False, ancilla_state=None):
+    """Run ``program`` on the basis columns ``col0 .. col0 + 2^n_cols_bits`` (ancillas in |0>, or in the
+    single-qubit pure state ``ancilla_state``, which is then also the state they are projected on).
 
     Returns the ``[rows][columns]`` block, rows restricted to ancilla bits = 0 when
     ``drop_ancilla``.  This is the column-batched unitary reconstruction that replaces
@@ -212,20 +253,15 @@ def simulate_columns(program: Program, col0: int, n_cols_bits: int, dtype=np.com
     n_bits = n + b
     anc = program.ancilla_mask
     state = eng.empty(1 << n_bits)
-    eng.init_basis_columns(state, n_bits, b, col0, anc)
+    eng.init_basis_columns(state, n_bits, b, col0, anc, ancilla_state)
     eng.upload(program, b)
     spare = None
-    if fuse:
-        try:
-            eng.fuse()
-            spare = eng.empty(1 << n_bits)
-        except QsvError as e:  # fusion pass refuses this program -> one kernel per gate (still CUDA)
-            if "not built" not in str(e) and "unsupported" not in str(e).lower():
-                raise
+    if fuse and _try_fuse(eng):
+        spare = eng.empty(1 << n_bits)
     res = eng.run(state, spare)
     rows_bits = n
     if drop_ancilla and anc:
-        res = eng.project_ancilla(res, n_bits, b, anc)
+        res = eng.project_ancilla(res, n_bits, b, anc, ancilla_state)
         rows_bits = n - bin(anc).count("1")
     if return_device:
         return res.view(1 << rows_bits, 1 << b)
@@ -233,13 +269,13 @@ def simulate_columns(program: Program, col0: int, n_cols_bits: int, dtype=np.com
     return res.view(1 << rows_bits, 1 << b).cpu().numpy()
 
 
-def reconstruct_unitary(gates_time_order, register=None, drop_ancilla=False, dtype=np.complex128, fuse=True):
+def reconstruct_unitary(gates_time_order, register=None, drop_ancilla=False, dtype=np.complex128, fuse=True, ancilla_state=None):
     """Dense operator of a CtrlGate stream over ``register`` (default: sorted union)."""
     program = flatten(gates_time_order, register)
     anc = program.ancilla_mask
     if drop_ancilla or not anc:
         n_free = program.n_qubits - bin(anc).count("1")
-        return simulate_columns(program, 0, n_free, dtype=dtype, fuse=fuse, drop_ancilla=True)
+        return simulate_columns(program, 0, n_free, dtype=dtype, fuse=fuse, drop_ancilla=True, ancilla_state=ancilla_state)
     # full operator including ancilla=1 columns: treat ancillas as ordinary qubits
     eng = get_engine(dtype)
     n = program.n_qubits
@@ -282,13 +318,8 @@ def apply_circuit(program: Program, states: np.ndarray, dtype=np.complex128, fus
     dev = torch.from_numpy(padded.reshape(-1)).to(f"cuda:{eng.device}")
     eng.upload(program, b)
     spare = None
-    if fuse:
-        try:
-            eng.fuse()
-            spare = torch.empty_like(dev)
-        except QsvError as e:
-            if "not built" not in str(e) and "unsupported" not in str(e).lower():
-                raise
+    if fuse and _try_fuse(eng):
+        spare = torch.empty_like(dev)
     res = eng.run(dev, spare)
     torch.cuda.synchronize(eng.device)
     out = res.view(dim, 1 << b).cpu().numpy()[:, :batch]

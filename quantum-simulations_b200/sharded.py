@@ -401,12 +401,9 @@ class GpuExecutor:
         eng.upload_records(recs, pool, n_loc, 0)
         fused = False
         if self.fuse and len(recs):
-            try:
-                self.fused_sweeps_per_apply += int(eng.fuse(self.tile_bits))
-                fused = True
-            except Exception as e:
-                if "unsupported" not in str(e).lower():
-                    raise
+            # (no per-gate downgrade here: a segment the fusion pass refuses is a planning error at these sizes)
+            self.fused_sweeps_per_apply += int(eng.fuse(self.tile_bits))
+            fused = True
         self.engines[key] = (eng, fused)
 
     def run_segment(self, key, state, spare):

@@ -86,15 +86,11 @@ class GpuChunkExecutor:
         eng = self.eng
         eng.upload_records(recs, pool, self.n_bits, self.batch_bits)
         spare = None
-        if self.fuse:
-            try:
-                eng.fuse()
-                if self.spare is None:
-                    self.spare = eng.empty(self.state.numel())
-                spare = self.spare
-            except QsvError as e:  # the fusion pass refuses this chunk -> one kernel per gate (still CUDA)
-                if "unsupported" not in str(e).lower():
-                    raise
+        from .engine import _try_fuse
+        if self.fuse and _try_fuse(eng):                 # (a refused chunk runs one kernel per gate, with a warning)
+            if self.spare is None:
+                self.spare = eng.empty(self.state.numel())
+            spare = self.spare
         res = eng.run(self.state, spare)
         if res is not self.state:
             self.state, self.spare = res, self.state

@@ -276,3 +276,44 @@ def test_fast_singlet_producer_reproduces_the_unitary():
         off = int(r["matrix_offset"])
         orc.apply_two_level(st2, (int(r["row0"]), int(r["row1"])), p2[off:off + 4].reshape(2, 2))
     assert np.abs(st2 - u).max() < 1e-12
+
+
+def test_trace_matches_reference_outcomes():
+    """CtrlGate.trace(qubit, state) on the gate's own core (cgate.py:228-287): same gate out -- qspace, roles, core matrix,
+    phase -- as the reference on 130 (gate, qubit, state) cases shaped like test_cgate.py:673-806, and an exception exactly
+    where the reference raises (its constructor rejects a non-unitary result)."""
+    from tests.golden_io import load, unpack_gates
+    d = load("trace")
+    src, res = unpack_gates(d, "src"), unpack_gates(d, "res")
+    accepted = 0
+    for i, (g, r) in enumerate(zip(src, res)):
+        q = g.qspace[int(d["which"][i])]
+        try:
+            got = g.trace(q, d["state"][i])
+            ok = True
+        except (AssertionError, NotImplementedError):
+            ok = False
+        assert ok == bool(d["ok"][i]), i
+        if ok:
+            accepted += 1
+            assert got.qspace == r.qspace
+            assert [int(c) for c in got.controls()] == [int(c) for c in r.controls()]
+            assert np.abs(got.matrix() - r.matrix()).max() < 1e-12
+            assert abs(got.phase() - r.phase()) < 1e-12
+    assert accepted == int(d["ok"].sum()) and accepted > 40
+
+
+def test_trace_argument_errors():
+    """Messages of test_cgate.py:716-741."""
+    import quantum_simulations_b200 as qs
+    g = qs.CtrlGate(np.array(qs.UnivGate.H), [qs.QType.CONTROL1, qs.QType.TARGET, qs.QType.CONTROL0],
+                    [qs.Qubit(0), qs.Qubit(1), qs.Qubit(2)])
+    with pytest.raises(AssertionError) as e:
+        g.trace(g.qspace[0], np.array([[1], [0]]))
+    assert str(e.value) == 'state vector must be a 1D array of length 2, but got (2, 1).'
+    with pytest.raises(AssertionError) as e:
+        g.trace(g.qspace[0], np.array([1, 1]))
+    assert str(e.value) == 'state vector must normalized but got [1 1].'
+    with pytest.raises(AssertionError) as e:
+        g.trace(qs.Qubit(10), np.array([1, 0]))
+    assert str(e.value) == 'Qubit q10 not in qspace.'
