@@ -72,6 +72,12 @@ struct Builder {
     std::vector<char> consumed;        // gates that belong to a recognised SWAP
     size_t next_gate = 0;              // index of the next unscheduled source gate (for look-ahead)
     uint64_t relabelled_gates = 0;
+    // Register bits per stage of the launch being emitted: RB (4) for the cp.async images, RB8 (3) when flush() tries the
+    // radix-8 TMA image first.  Arrays stay sized for RB; with rb = 3 register bit 3 simply never occurs.
+    int rb = RB;
+    bool tma_swizzle = false;          // tile slots follow the TMA engine's 128-byte swizzle instead of swz()
+    bool allow8 = true;                // (sweep_plan_build_host: complex128, QSV_NO_FFT8 unset)
+    uint32_t sw(uint32_t l) const { return tma_swizzle ? swz128(l) : swz(l); }
 
     Builder(qsv_ctx* c, SweepPlan* p, int n_, int k_) : ctx(c), plan(p), n(n_), k(k_) {
         c_low = (k < n) ? std::min(4, k - 1) : 0;
@@ -284,12 +290,12 @@ struct Builder {
         SwOp op;
         memset(&op, 0, sizeof(op));
         op.type = OP_STAGE;
-        for (int q = 0; q < RB; ++q) op.st.rpos[q] = (uint8_t)sc.rloc[q];
-        for (int j = 0; j < NREG; ++j) {
+        for (int q = 0; q < rb; ++q) op.st.rpos[q] = (uint8_t)sc.rloc[q];
+        for (int j = 0; j < (1 << rb); ++j) {
             uint32_t off = 0;
-            for (int q = 0; q < RB; ++q)
+            for (int q = 0; q < rb; ++q)
                 if ((j >> q) & 1) off |= 1u << sc.rloc[q];
-            op.st.roffsw[j] = (uint16_t)swz(off);
+            op.st.roffsw[j] = (uint16_t)sw(off);
         }
         if (e.first_rloc.empty()) e.first_rloc = sc.rloc;
         e.last_rloc = sc.rloc;
@@ -531,7 +537,7 @@ struct Builder {
     void finish_stage_regs(StageCtx& sc, const std::vector<int>& want) {
         // register bits: the wanted local bits, padded with the highest free local bits
         std::vector<int> r = want;
-        for (int l = k - 1; l >= 0 && (int)r.size() < RB; --l)
+        for (int l = k - 1; l >= 0 && (int)r.size() < rb; --l)
             if (std::find(r.begin(), r.end(), l) == r.end()) r.push_back(l);
         std::sort(r.begin(), r.end());
         sc.rloc = r;
@@ -618,10 +624,11 @@ struct Builder {
                 }
             }
             const int nh = (int)order.size();
-            for (int q = RB - 1; q >= 0; --q)  // the other register bits keep their relative order below the butterfly bits
+            for (int q = rb - 1; q >= 0; --q)  // the other register bits keep their relative order below the butterfly bits
                 if (std::find(order.begin(), order.end(), q) == order.end()) order.push_back(q);
             int newbit[RB];  // old register bit -> new register bit
-            for (int r = 0; r < RB; ++r) newbit[order[r]] = RB - 1 - r;
+            for (int r = 0; r < RB; ++r) newbit[r] = r;   // (rb = 3: bit 3 does not exist and maps to itself)
+            for (int r = 0; r < rb; ++r) newbit[order[r]] = rb - 1 - r;
             auto map_j = [&](int j) {
                 int r = 0;
                 for (int q = 0; q < RB; ++q)
@@ -634,10 +641,10 @@ struct Builder {
             f.fs.scale = 1.0;
             f.fs.hmask = (uint8_t)nh;
             for (int s_ = 0; s_ <= RB; ++s_) f.fs.tslot[s_] = f.fs.gslot[s_] = NONE16;
-            for (int q = 0; q < RB; ++q) {
-                f.fs.abit[q] = 0xFF;
+            for (int q = 0; q < RB; ++q) f.fs.abit[q] = 0xFF;
+            for (int q = 0; q < rb; ++q) {
                 f.fs.rpos[q] = st.st.rpos[q];
-                f.fs.boff[newbit[q]] = (uint16_t)swz(1u << st.st.rpos[q]);
+                f.fs.boff[newbit[q]] = (uint16_t)sw(1u << st.st.rpos[q]);
             }
             for (int q = 0; q < 3; ++q) f.fs.w_off[q] = NONE16;
             // ---- pass 2: tables
@@ -653,18 +660,18 @@ struct Builder {
                 memcpy(&tab[2 * o->w.w_off], perm, sizeof(perm));
                 if (!fft_table_shape(tab, o->w.w_off, A)) FS_NO("a phase table couples bits outside the FFT shape");
                 if (A > 0 && o->w.wmask) {
-                    f.fs.w_off[3 - A] = o->w.w_off;
+                    f.fs.w_off[rb - 1 - A] = o->w.w_off;
                     any_w = true;
                 }
             }
             if (any_w)
-                for (int q = 0; q < 3; ++q)
+                for (int q = 0; q < rb - 1; ++q)
                     if (f.fs.w_off[q] == NONE16) f.fs.w_off[q] = ones_table(one_w, NREG);
             // ---- deferred phases
             if (tw) {
                 f.fs.scale = tw->tw.scale;
                 bool any_bit = false;
-                for (int q = 0; q < RB; ++q)
+                for (int q = 0; q < rb; ++q)
                     if (tw->tw.abit[q] != 0xFF) {
                         const int nq = newbit[q];
                         f.fs.abit[nq] = (uint8_t)nq;
@@ -681,12 +688,13 @@ struct Builder {
                 if (c0) f.fs.flags |= 4;
                 // every factor the kernel reads unconditionally must point somewhere: absent ones at all-ones slots
                 for (int nq = 0; nq <= RB; ++nq) {
-                    const bool used = nq == RB ? c0 : (any_bit && (f.fs.abit[nq] != 0xFF || nq >= RB - nh));
+                    if (nq >= rb && nq < RB) continue;
+                    const bool used = nq == RB ? c0 : (any_bit && (f.fs.abit[nq] != 0xFF || nq >= rb - nh));
                     if (!used) continue;
                     if (f.fs.tslot[nq] == NONE16) f.fs.tslot[nq] = ones_table(one_t, TSLOT_LEN);
                     if (f.fs.gslot[nq] == NONE16) f.fs.gslot[nq] = ones_gslot();
                 }
-                for (int nq = RB - nh; nq < RB; ++nq)
+                for (int nq = rb - nh; nq < rb; ++nq)
                     if (any_bit) f.fs.abit[nq] = (uint8_t)nq;
             }
             f.tgt = (uint8_t)(2 * nh + (any_w ? 1 : 0));  // shape code (added to DC_FSTAGE at conversion)
@@ -700,12 +708,89 @@ struct Builder {
         e.gslots.swap(gslots);
         // the direct store enumerates the last stage's register bits by (new) register index
         if (!e.last_rloc.empty()) {
-            std::vector<int> r(RB);
-            for (int rnk = 0; rnk < RB; ++rnk) r[RB - 1 - rnk] = e.last_rloc[last_order[rnk]];
+            std::vector<int> r(rb);
+            for (int rnk = 0; rnk < rb; ++rnk) r[rb - 1 - rnk] = e.last_rloc[last_order[rnk]];
             e.last_rloc = r;
         }
         return true;
     }
+
+    // How the TMA engine sees a tile whose bits sit at the index positions `bits_at` (ascending): false when the bit runs
+    // cannot be described (needs index bits 0..2 in the tile and at most TMA_MAX_INST instructions of five dimensions).
+    bool build_tma(const std::vector<int>& bits_at, TmaTile& T) const {
+        memset(&T, 0, sizeof(T));
+        if (k < 4 || k > 11 || (int)bits_at.size() != k || bits_at[0] != 0 || bits_at[1] != 1 || bits_at[2] != 2) return false;
+        std::vector<std::pair<int, int>> runs;  // (first index bit, length), ascending, at most 8 bits each (box extent <= 256)
+        for (int l = 3; l < k; ++l) {
+            const int b = bits_at[l];
+            if (!runs.empty() && runs.back().first + runs.back().second == b && runs.back().second < 8) runs.back().second++;
+            else runs.push_back({b, 1});
+        }
+        std::vector<int> inst_bits;  // index bits walked by separate instructions (the top tile bits)
+        while (runs.size() > 4) {
+            auto& r = runs.back();
+            inst_bits.insert(inst_bits.begin(), r.first + r.second - 1);
+            if (--r.second == 0) runs.pop_back();
+        }
+        if (runs.empty() || runs[0].first != 3 || (1 << inst_bits.size()) > TMA_MAX_INST) return false;
+        T.rank = 1 + (int)runs.size();
+        T.box[0] = 16;
+        T.size[0] = 16;
+        T.shift[0] = 0;
+        T.bits[0] = 3;
+        int in_dims = 3;
+        for (size_t d = 0; d < runs.size(); ++d) {
+            const int s0 = runs[d].first, s1 = d + 1 < runs.size() ? runs[d + 1].first : n;
+            if (s1 - s0 > 31) return false;  // (coordinates are signed 32-bit)
+            T.shift[d + 1] = (uint8_t)s0;
+            T.bits[d + 1] = (uint8_t)(s1 - s0);
+            T.box[d + 1] = 1u << runs[d].second;
+            T.size[d + 1] = 1ull << (s1 - s0);
+            T.stride_bytes[d + 1] = 16ull << s0;
+            in_dims += runs[d].second;
+        }
+        T.n_inst = 1 << inst_bits.size();
+        T.inst_amps = 1u << in_dims;
+        for (int e_ = 0; e_ < T.n_inst; ++e_)
+            for (size_t i = 0; i < inst_bits.size(); ++i)
+                if ((e_ >> i) & 1) T.inst_goff[e_] |= 1ull << inst_bits[i];
+        return true;
+    }
+
+    // Everything the radix-8 image needs for the launch in `e` (after to_fstages): load / store views of the tile, and for a
+    // permuting store the re-ordering of the tile by the last stage.
+    bool build_sweep8(const Emit& e, const std::vector<int>* out_pos_of_phys, Sweep8Extra& X) const {
+        memset(&X, 0, sizeof(X));
+        if (!build_tma(tile_pos, X.in)) return false;
+        X.out = X.in;
+        if (!out_pos_of_phys) return true;
+        std::vector<int> out_at(k), order(k), rank_of(k);
+        for (int l = 0; l < k; ++l) {
+            out_at[l] = (*out_pos_of_phys)[tile_pos[l]];
+            order[l] = l;
+        }
+        std::sort(order.begin(), order.end(), [&](int x, int y) { return out_at[x] < out_at[y]; });
+        std::vector<int> sorted_out(k);
+        bool identity = true;
+        for (int u = 0; u < k; ++u) {
+            sorted_out[u] = out_at[order[u]];
+            rank_of[order[u]] = u;
+            identity &= order[u] == u;
+        }
+        if (!build_tma(sorted_out, X.out)) return false;
+        if (identity) return true;  // the tile keeps its order in shared memory; only the addresses differ
+        X.permuting = 1;
+        X.loc_perm = make_segmap(rank_of);
+        // the last stage's register bit q sits at tile bit p_q (recovered from its slot offset: the swizzle only adds lower bits)
+        const SwOp& last = e.ops.back();
+        for (int q = 0; q < RB8; ++q) {
+            const int p_q = 31 - __builtin_clz((unsigned)last.fs.boff[q]);
+            X.boff_out[q] = (uint16_t)swz128(1u << rank_of[p_q]);
+        }
+        return true;
+    }
+
+    static constexpr int RETRY_RB4 = -1000;  // internal: the radix-8 attempt of flush() cannot hold this launch
 
     int push_sweep(Emit& e, bool out_of_place, const std::vector<int>* out_pos_of_phys) {
         const bool has_work = std::any_of(e.ops.begin(), e.ops.end(), [](const SwOp& o) { return o.type != OP_STAGE; });
@@ -719,6 +804,12 @@ struct Builder {
             return qsv_fail(ctx, QSV_E_TOOBIG, "internal: sweep budget exceeded (%zu ops, %zu slots, %zu table entries)", e.ops.size(),
                             e.gslots.size(), e.tab.size() / 2);
         const bool all_fft = has_work && to_fstages(e);
+        Sweep8Extra extra8;
+        if (rb == RB8) {
+            // the radix-8 image runs FFT-shaped launches only, a handful of stages and scalars, on tiles the TMA engine can
+            // move; nothing has been committed to the plan yet, so flush() can start over with four register bits
+            if (!all_fft || e.ops.size() > MAX_OPS8 || e.gslots.size() > MAX_GSLOT8 || !build_sweep8(e, out_pos_of_phys, extra8)) return RETRY_RB4;
+        }
         SweepParams* sp = new SweepParams();
         memset(sp, 0, sizeof(*sp));
         SweepDesc& D = sp->d;
@@ -757,7 +848,7 @@ struct Builder {
         D.in_loc = make_segmap(in_dst);
         D.out_loc = make_segmap(out_dst);
         D.st_enum = make_segmap(enum_dst);
-        D.tb = std::max(5, k - RB);
+        D.tb = std::max(5, k - rb);
         // direct global <-> register paths: need full tiles (k >= 9) and a stage whose register bits
         // leave the lowest local bits to the lanes, so that the accesses stay coalesced
         auto high_only = [](const std::vector<int>& r) { return !r.empty() && *std::min_element(r.begin(), r.end()) >= 4; };
@@ -768,8 +859,8 @@ struct Builder {
             std::vector<int> lr = e.last_rloc;  // (register order of an OP_FSTAGE stage is not position order)
             std::sort(lr.begin(), lr.end());
             for (int q = 0; q < RB; ++q) {
-                D.first_rpos[q] = (uint8_t)(e.first_rloc.empty() ? q : e.first_rloc[q]);
-                D.last_rpos[q] = (uint8_t)(lr.empty() ? q : lr[q]);
+                D.first_rpos[q] = (uint8_t)(e.first_rloc.empty() || q >= rb ? q : e.first_rloc[q]);
+                D.last_rpos[q] = (uint8_t)(lr.empty() || q >= rb ? q : lr[q]);
             }
         }
         auto dep = [&](uint32_t l, const std::vector<int>& dstpos) {
@@ -783,20 +874,21 @@ struct Builder {
             uint32_t l_ld;
             if (D.direct_load) {
                 l_ld = 0;
-                for (int q = 0; q < RB; ++q)
+                for (int q = 0; q < rb; ++q)
                     if ((i >> q) & 1) l_ld |= 1u << e.first_rloc[q];
             } else {
                 l_ld = (uint32_t)i << D.tb;
             }
             if (l_ld < (1u << k)) {
                 D.ld_goff[i] = dep(l_ld, in_dst);
-                D.ld_soff[i] = (uint16_t)swz(l_ld);
+                D.ld_soff[i] = (uint16_t)sw(l_ld);
             }
             // store side
             uint32_t l_st;
             if (D.direct_store) {
+                if (i >= (1 << rb)) continue;
                 l_st = 0;
-                for (int q = 0; q < RB; ++q)
+                for (int q = 0; q < rb; ++q)
                     if ((i >> q) & 1) l_st |= 1u << e.last_rloc[q];
             } else {
                 const uint32_t u = (uint32_t)i << D.tb;
@@ -806,7 +898,7 @@ struct Builder {
                     if ((u >> b) & 1) l_st |= 1u << enum_dst[b];
             }
             D.st_goff[i] = dep(l_st, out_dst);
-            D.st_soff[i] = (uint16_t)swz(l_st);
+            D.st_soff[i] = (uint16_t)sw(l_st);
         }
         {
             std::vector<int> gin(glob_pos.size()), gout(glob_pos.size());
@@ -844,8 +936,9 @@ struct Builder {
         s.fused = true;
         s.params = sp;
         s.out_of_place = out_of_place;
-        s.img = all_fft ? IMG_FFT : all_lean ? IMG_LEAN : IMG_FULL;
+        s.img = all_fft ? (rb == RB8 ? IMG_FFT8 : IMG_FFT) : all_lean ? IMG_LEAN : IMG_FULL;
         s.n_gates = e.n_gates;
+        if (s.img == IMG_FFT8) s.tma = new Sweep8Extra(extra8);
         plan->steps.push_back(s);
         e = Emit();
         return QSV_OK;
@@ -856,6 +949,40 @@ struct Builder {
             cur_targets = 0;
             return QSV_OK;
         }
+        // Radix-8 TMA image first when the sweep's butterfly targets fill one or two three-bit stages as well as they
+        // would fill four-bit ones (1-3 or 5-6 targets); anything that does not fit it starts over with four register bits.
+        int n_t = 0;
+        {
+            uint64_t seen = 0;
+            for (size_t gi : cur)
+                if (pg[gi].kind != QSV_DIAG1) seen |= 1ull << pg[gi].target_bits[0];
+            n_t = __builtin_popcountll(seen);
+        }
+        const bool try8 = allow8 && k < n && k >= 9 && k <= 11 && n_t >= 1 && n_t <= 6 && n_t != 4;
+        if (try8) {
+            const size_t steps0 = plan->steps.size(), aux0 = plan->aux.size();
+            const uint64_t targets0 = cur_targets;
+            const double scale0 = sweep_scale;
+            rb = RB8;
+            tma_swizzle = true;
+            const int rc = flush_emit();
+            rb = RB;
+            tma_swizzle = false;
+            if (rc != RETRY_RB4) return rc;
+            while (plan->steps.size() > steps0) {
+                delete plan->steps.back().params;
+                delete plan->steps.back().tma;
+                plan->steps.pop_back();
+            }
+            plan->aux.resize(aux0);
+            cur_targets = targets0;
+            sweep_scale = scale0;
+            pend = Pending();
+        }
+        return flush_emit();
+    }
+
+    int flush_emit() {
         // Can the permutation that the remaining SWAP relabels call for ride on this sweep's store?  It can
         // when the tile also holds the bits that become the low (coalescing) bits of the output.
         std::vector<int> P;
@@ -884,12 +1011,12 @@ struct Builder {
                 if (g.kind == QSV_DIAG1) continue;
                 const int l = loc_of[g.target_bits[0]];
                 if (std::find(want.begin(), want.end(), l) != want.end()) continue;
-                if ((int)want.size() == RB) break;
+                if ((int)want.size() == rb) break;
                 want.push_back(l);
             }
             // diagonal gates prefer a register bit of their own: if the stage has room, give pair gates one
-            if ((int)want.size() < RB) {
-                for (size_t q = i; q < j && (int)want.size() < RB; ++q) {
+            if ((int)want.size() < rb) {
+                for (size_t q = i; q < j && (int)want.size() < rb; ++q) {
                     const qsv_gate_t& g = pg[cur[q]];
                     if (g.kind != QSV_DIAG1 || __builtin_popcountll(g.ctrl_mask) != 1) continue;
                     const int t = g.target_bits[0], cb = __builtin_ctzll(g.ctrl_mask);
@@ -975,6 +1102,7 @@ struct Builder {
             i = j;
         }
         int rc = push_sweep(e, fold, fold ? &P : nullptr);
+        if (rc) return rc;   // (RETRY_RB4 included: nothing below may happen before the launch is really in the plan)
         if (fold) apply_permutation(P);
         cur.clear();
         cur_targets = 0;
@@ -1003,6 +1131,8 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan)
         plan->aux.resize(2, 0.0);  // offset 0 reserved
         Builder b(ctx, plan, n, k);
         b.target_cap = cap;
+        static const bool no8 = getenv("QSV_NO_FFT8") != nullptr;  // A/B aid: keep every launch in the cp.async images
+        b.allow8 = ctx->dtype == QSV_C128 && !no8;
         int rc = QSV_OK;
         for (size_t i = 0; i < ctx->gates.size() && !rc; ++i) rc = b.add_gate(i);
         if (!rc) {
@@ -1044,6 +1174,15 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan)
             delete best;
             best = p;
         }
+    }
+    if (getenv("QSV_PLAN_DEBUG")) {
+        static const char* names[] = {"full", "lean", "fft16", "fft8-tma"};
+        for (auto& st : best->steps)
+            if (st.fused)
+                fprintf(stderr, "[qsv] sweep: image %s, %d ops, %d scalars, %llu gates%s%s\n", names[st.img], st.params->d.n_ops, st.params->d.n_gslots,
+                        (unsigned long long)st.n_gates, st.out_of_place ? ", permuting store" : "",
+                        st.img == IMG_FFT8 ? (st.tma->permuting ? ", tile re-ordered for the TMA store" : ", TMA store")
+                                           : (st.params->d.direct_store ? ", direct store" : ""));
     }
     *out_plan = best;
     return QSV_OK;

@@ -14,6 +14,83 @@
 // global offsets, per-tile scalars).  It exists so that the planner -- stage selection, phase polynomials,
 // relabelling, budgets, FFT-shape conversion -- can be fuzzed against the oracle on a machine without a GPU.
 // It is not a compute path: nothing in the package calls it, and it refuses states of more than 2^22 amplitudes.
+// The radix-8 / TMA image (qsv_sweep8.cu), restated: the tile copies follow the TmaTile descriptions the way the engine
+// does (box coordinates from the tile id, 128-byte rows, SWIZZLE_128B slots), the stages run fstage8_compute /
+// fstage8_put thread by thread, and a permuting launch re-orders the tile before the store like the kernel's last stage.
+template <typename R>
+static int sweep8_emulate_host(qsv_ctx* ctx, const SweepParams& P, const Sweep8Extra& X, const std::vector<double>& auxv,
+                               const typename cplx_of<R>::type* src, typename cplx_of<R>::type* dst) {
+    typedef typename cplx_of<R>::type C;
+    const SweepDesc& D = P.d;
+    const int k = D.k;
+    if (sizeof(C) != 16) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: the radix-8 image is complex128 only");
+    if (D.n_ops > MAX_OPS8 || D.n_gslots > MAX_GSLOT8) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: %d ops / %d scalars in a radix-8 launch", D.n_ops, D.n_gslots);
+    const uint32_t tile_amps = 1u << k, threads = 1u << (k - RB8);
+    const uint64_t n_tiles = 1ull << (D.n_bits - k);
+    const double2* aux2 = reinterpret_cast<const double2*>(auxv.data());
+    std::vector<C> tile_v(tile_amps);
+    C* tile = tile_v.data();
+    std::vector<double2> smE(MAX_GSLOT8), smT(MAX_TAB);
+    for (uint32_t i = 0; i < D.tab_len; ++i) smT[i] = aux2[D.tab_off + i];
+    auto engine_copy = [&](const TmaTile& T, uint64_t phys_tile, bool load, const C* g_in, C* g_out) {
+        int box_bits[5] = {3, 0, 0, 0, 0};
+        for (int d = 1; d < T.rank; ++d) box_bits[d] = __builtin_ctz(T.box[d]);
+        for (int e = 0; e < T.n_inst; ++e) {
+            const uint64_t p = phys_tile | T.inst_goff[e];
+            uint64_t c[5] = {0, 0, 0, 0, 0};
+            for (int d = 1; d < T.rank; ++d) c[d] = (p >> T.shift[d]) & ((1ull << T.bits[d]) - 1ull);
+            for (uint32_t l = 0; l < T.inst_amps; ++l) {
+                // box element l (dimension 0 fastest) -> byte address in the tensor = sum coordinate x stride
+                uint64_t byte = (uint64_t)(l & 7u) * 16;
+                uint32_t rest = l >> 3;
+                for (int d = 1; d < T.rank; ++d) {
+                    const uint64_t x = c[d] + (rest & (T.box[d] - 1u));
+                    if (x >= T.size[d]) return false;
+                    byte += x * T.stride_bytes[d];
+                    rest >>= box_bits[d];
+                }
+                const uint32_t slot = swz128(e * T.inst_amps + l);
+                if (load) tile[slot] = g_in[byte / 16];
+                else g_out[byte / 16] = tile[slot];
+            }
+        }
+        return true;
+    };
+    std::vector<C> regs((size_t)threads * NREG8);
+    for (uint64_t t = 0; t < n_tiles; ++t) {
+        for (uint32_t gs = 0; gs < (uint32_t)D.n_gslots; ++gs) {
+            const double2* gt = aux2 + D.gtab_off + (size_t)gs * D.g_chunks * 16;
+            double2 e = gt[t & 15ull];
+            for (int c = 1; c < D.g_chunks; ++c) e = cmul(e, gt[c * 16 + ((t >> (4 * c)) & 15ull)]);
+            smE[gs] = e;
+        }
+        if (!engine_copy(X.in, seg_apply64x(t, D.in_glob), true, src, nullptr)) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: TMA load box leaves the tensor");
+        for (int i = 0; i < D.n_ops; ++i) {
+            const OpView op{&P.ops[i]};
+            if (op.type() < DC_FSTAGE || op.type() >= DC_FSTAGE + 8) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: op %d of a radix-8 launch is not a radix-8 OP_FSTAGE", i);
+            const bool reorder = i == D.n_ops - 1 && X.permuting;
+            // (a stage reads all its slots before it writes them, and threads own disjoint slots: threads in sequence are exact;
+            // the re-ordering stage writes other threads' slots, so it computes everything first -- the kernel's extra barrier)
+            for (uint32_t tid = 0; tid < threads; ++tid) {
+                const uint32_t bl = expand_rb8(tid, op.rpos(0), op.rpos(1), op.rpos(2));
+                C w[NREG8];
+                fstage8_compute<C, R>(op, tile, smT.data(), smE.data(), tid, swz128(bl), w);
+                if (!reorder) fstage8_put<C>(tile, swz128(bl), op.boff(0), op.boff(1), op.boff(2), w);
+                else for (int j = 0; j < NREG8; ++j) regs[(size_t)tid * NREG8 + j] = w[j];
+            }
+            if (reorder)
+                for (uint32_t tid = 0; tid < threads; ++tid) {
+                    const uint32_t bl = expand_rb8(tid, op.rpos(0), op.rpos(1), op.rpos(2));
+                    C w[NREG8];
+                    for (int j = 0; j < NREG8; ++j) w[j] = regs[(size_t)tid * NREG8 + j];
+                    fstage8_put<C>(tile, swz128(seg_apply(bl, X.loc_perm)), X.boff_out[0], X.boff_out[1], X.boff_out[2], w);
+                }
+        }
+        if (!engine_copy(X.out, seg_apply64x(t, D.out_glob), false, nullptr, dst)) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: TMA store box leaves the tensor");
+    }
+    return QSV_OK;
+}
+
 template <typename R>
 static int sweep_emulate_host(qsv_ctx* ctx, const SweepParams& P, const std::vector<double>& auxv, int img,
                               const typename cplx_of<R>::type* src, typename cplx_of<R>::type* dst) {
@@ -151,11 +228,12 @@ static int hostcheck_run(qsv_ctx* ctx, SweepPlan* plan, void* state, uint64_t* o
     for (auto& st : plan->steps) {
         if (!st.fused) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "hostcheck: the plan holds a gate that is not fused (dense-k / row pair)");
         C* d = st.out_of_place ? other : cur;
-        int rc = sweep_emulate_host<R>(ctx, *st.params, plan->aux, st.img, cur, d);
+        int rc = st.img == IMG_FFT8 ? sweep8_emulate_host<R>(ctx, *st.params, *st.tma, plan->aux, cur, d)
+                                    : sweep_emulate_host<R>(ctx, *st.params, plan->aux, st.img, cur, d);
         if (rc) return rc;
         if (st.out_of_place) std::swap(cur, other);
         ++sweeps;
-        fft += st.img == IMG_FFT;
+        fft += st.img == IMG_FFT || st.img == IMG_FFT8;
     }
     if (cur != static_cast<C*>(state)) memcpy(state, cur, amps * sizeof(C));
     if (out_sweeps) *out_sweeps = sweeps;
@@ -193,7 +271,7 @@ extern "C" int qsv_hostcheck_fused(int dtype, int n_bits, const qsv_gate_t* gate
         uint64_t sweeps = 0, fft = 0;
         for (auto& st : plan->steps) {
             sweeps += st.fused;
-            fft += st.fused && st.img == IMG_FFT;
+            fft += st.fused && (st.img == IMG_FFT || st.img == IMG_FFT8);
         }
         if (out_sweeps) *out_sweeps = sweeps;
         if (out_fft_sweeps) *out_fft_sweeps = fft;

@@ -259,6 +259,9 @@ void sweep_plan_free(SweepPlan* p) { delete p; }
 
 
 static int sweep_set_smem_attr(qsv_ctx* ctx, int k);
+// qsv_sweep8.cu: the radix-8 / TMA image
+int sweep8_prepare(qsv_ctx* ctx, int k);
+int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const double* d_aux, const PlanStep& st, cudaStream_t stream);
 
 int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
     SweepPlan* plan = nullptr;
@@ -281,6 +284,15 @@ int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
             return rc2;
         }
     }
+    for (auto& st : plan->steps)
+        if (st.fused && st.img == IMG_FFT8) {
+            int rc3 = sweep8_prepare(ctx, k);
+            if (rc3) {
+                delete plan;
+                return rc3;
+            }
+            break;
+        }
     ctx->plan = plan;
     if (out_sweeps) {
         uint64_t s = 0;
@@ -388,7 +400,8 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
             QSV_CUDA(ctx, cudaEventRecord(ev0, stream));
         }
         {
-            int rc = sweep_launch(ctx, n, k, cur, dstp, plan->d_aux, *st.params, stream, st.img);
+            int rc = st.img == IMG_FFT8 ? sweep8_launch(ctx, n, k, cur, dstp, plan->d_aux, st, stream)
+                                        : sweep_launch(ctx, n, k, cur, dstp, plan->d_aux, *st.params, stream, st.img);
             if (rc) return rc;
         }
         static const bool sync_each = getenv("QSV_SYNC") != nullptr;  // debugging aid: surface kernel faults at the launch site

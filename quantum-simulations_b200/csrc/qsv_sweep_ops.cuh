@@ -17,6 +17,15 @@
     (2 * ((size_t)(amp_bytes) << (k)) + (2 * MAX_GSLOT + MAX_TAB) * sizeof(double2) + (size_t)PARK_WORDS * (threads) * sizeof(uint64_t))
 #define TSLOT_LEN 32     // one thread-phase slot = 2 chunks x 16 entries
 #define MAX_SEG 12
+// Radix-8 image (IMG_FFT8, qsv_sweep8.cu): 3 register bits per stage, 8 amplitudes per thread, tiles moved by TMA
+#define RB8 3
+#define NREG8 8
+#define MAX_OPS8 8       // stages per launch (an FFT-shaped launch is one op per stage)
+#define MAX_GSLOT8 16    // per-tile phase scalars per launch of the radix-8 image
+#define PARK8_OPS 2      // stages whose per-thread slot constants are parked in shared memory (later ones recompute them)
+#define TMA_MAX_INST 16  // cp.async.bulk.tensor instructions per tile when the tile's bit runs need more than 5 dimensions
+#define SWEEP8_SMEM(k, threads) \
+    (2 * ((size_t)16 << (k)) + (2 * MAX_GSLOT8 + MAX_TAB) * sizeof(double2) + (size_t)(threads) * 4 * (PARK8_OPS + 1) + 32)
 
 enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_W = 4, OP_TWID = 5, OP_HADD = 6, OP_HW = 7, OP_FSTAGE = 8 };
 // Dispatch codes (SwOp::type as stored): the host resolves op kind, target register bit, real/complex
@@ -139,6 +148,35 @@ __host__ __device__ __forceinline__ uint64_t seg_apply64x(uint64_t x, const SegM
     return r;
 }
 __host__ __device__ __forceinline__ uint32_t swz(uint32_t l) { return l ^ (((l >> 3) ^ (l >> 6) ^ (l >> 9)) & 7u); }
+// The TMA engine's SWIZZLE_128B on 16-byte amplitudes: inside every 1 KB block (8 rows of 128 B) the 16-byte chunk index is
+// XOR-ed with the row number -- slot of local index l in a tile buffer aligned to 1 KB.  Like swz() it is linear over GF(2).
+__host__ __device__ __forceinline__ uint32_t swz128(uint32_t l) { return l ^ ((l >> 3) & 7u); }
+
+// How one tile of a sweep is described to the TMA engine (complex128 only).  The state is viewed as a tensor of up to five
+// dimensions over FLOAT64 elements: dimension 0 is (re, im) x index bits 0..2 = one 128-byte row; every further dimension d
+// covers the index bits [shift[d], shift[d] + bits[d]), whose lowest log2(box[d]) bits are tile bits (the box spans them)
+// and whose other bits come from the tile id (the start coordinate).  Tile bits that do not fit five dimensions are walked
+// by n_inst instructions, each with its own index offset and shared-memory offset.  Box elements land in shared memory in
+// ascending order of the tile bits' positions (bit i of the slot number before the swizzle = i-th lowest tile bit).
+struct TmaTile {
+    int rank, n_inst;
+    uint32_t box[5];
+    uint64_t size[5], stride_bytes[5];
+    uint8_t shift[5], bits[5];
+    uint64_t inst_goff[TMA_MAX_INST];   // index offset (amplitudes) of instruction e; its box goes to tile + e * inst_amps
+    uint32_t inst_amps;
+};
+
+// What a radix-8 launch needs beyond the SweepDesc: the engine's view of the tile on load and on store (different for a
+// bit-permuting sweep: the tile goes out in the order of its OUTPUT positions) and, for the permuting case, how the last
+// stage re-orders the tile in shared memory -- input-local index -> output-local index is a bit permutation (loc_perm), so
+// the output slots keep the XOR structure: slot of register 0 plus one offset per register bit (boff_out).
+struct Sweep8Extra {
+    TmaTile in, out;
+    int permuting;
+    SegMap loc_perm;
+    uint16_t boff_out[RB8];
+};
 
 // An op held in registers: header words + 64-byte payload (all accesses statically indexed).
 struct OpR {
@@ -447,6 +485,157 @@ __host__ __device__ __forceinline__ bool fstage_op(const OpR& op, C* __restrict_
     return false;
 }
 
+// ---- radix-8 stages (IMG_FFT8) ---------------------------------------------------------------------------------------
+// The same OP_FSTAGE record with three register bits: butterflies on register bits 2, 1, 0 in that order, the table after
+// the butterfly on bit A multiplies the registers with bit A set by a factor that depends on the bits below A (3 + 2
+// multiplies), then the deferred phases of bits 2, 1, 0.  8 amplitudes = 32 registers per thread, so that 256-thread CTAs
+// stay under 85 registers and three of them (24 warps) share an SM.
+template <typename C, int N, int A>
+__host__ __device__ __forceinline__ void hadd_n(C (&v)[N]) {
+#pragma unroll
+    for (int j0 = 0; j0 < N; ++j0)
+        if (!(j0 & (1 << A))) {
+            const int j1 = j0 | (1 << A);
+            const C a0 = v[j0], a1 = v[j1];
+            v[j0].x = a0.x + a1.x;
+            v[j0].y = a0.y + a1.y;
+            v[j1].x = a0.x - a1.x;
+            v[j1].y = a0.y - a1.y;
+        }
+}
+template <typename C, int N, int A>
+__host__ __device__ __forceinline__ void mul_bit_n(C (&v)[N], const double2 e) {
+    typedef decltype(v[0].x) R;
+    const C ee = cmake<C, R>((R)e.x, (R)e.y);
+#pragma unroll
+    for (int j = 0; j < N; ++j)
+        if (j & (1 << A)) v[j] = cmul(v[j], ee);
+}
+
+// An op record read where it lies.  In k_sweep8 the records sit in kernel-parameter (constant-bank) space, so every field is
+// ONE load of its own width -- no 96-byte fetch, no shift-and-mask extraction.  Offsets are those of OpR (payload-relative).
+struct OpView {
+    const SwOp* o;
+    __host__ __device__ __forceinline__ const unsigned char* pay() const { return reinterpret_cast<const unsigned char*>(o) + 24; }
+    __host__ __device__ __forceinline__ uint32_t type() const { return o->type; }
+    __host__ __device__ __forceinline__ uint32_t u16_at(int off) const { return *reinterpret_cast<const uint16_t*>(pay() + off); }
+    __host__ __device__ __forceinline__ uint32_t u8_at(int off) const { return pay()[off]; }
+    __host__ __device__ __forceinline__ double m(int i) const { return *reinterpret_cast<const double*>(pay() + 8 * i); }
+    __host__ __device__ __forceinline__ uint32_t tw_tslot(int s_) const { return u16_at(8 + 2 * s_); }
+    __host__ __device__ __forceinline__ uint32_t tw_gslot(int s_) const { return u16_at(8 + 2 * (RB + 1) + 2 * s_); }
+    __host__ __device__ __forceinline__ uint32_t tw_abit(int s_) const { return u8_at(8 + 4 * (RB + 1) + s_); }
+    __host__ __device__ __forceinline__ uint32_t rpos(int q) const { return u8_at(42 + q); }
+    __host__ __device__ __forceinline__ uint32_t boff(int q) const { return u16_at(46 + 2 * q); }
+};
+
+template <typename C, int B, typename OP>
+__host__ __device__ __forceinline__ void twid8_bit(C (&v)[NREG8], const OP& op, const double2* __restrict__ smT, const double2* __restrict__ smE,
+                                                   const uint32_t c_lo, const uint32_t c_hi) {
+    const uint32_t gsl = op.tw_gslot(B), tsl = op.tw_tslot(B);
+    mul_bit_n<C, NREG8, B>(v, cmul(smE[gsl], cmul(smT[tsl + c_lo], smT[tsl + c_hi])));
+}
+
+template <typename C, typename R, int NH, bool HAS_W, typename OP>
+__host__ __device__ __forceinline__ void fstage8_math(C (&v)[NREG8], const OP& op, const double2* __restrict__ smT,
+                                                      const double2* __restrict__ smE, const uint32_t tid) {
+    if constexpr (NH >= 1) {
+        hadd_n<C, NREG8, 2>(v);
+        if constexpr (HAS_W) {
+            const double2* w = smT + op.u16_at(36) + 4;
+#pragma unroll
+            for (int m = 1; m < 4; ++m) {
+                const double2 e = w[m];
+                v[4 + m] = cmul(v[4 + m], cmake<C, R>((R)e.x, (R)e.y));
+            }
+        }
+    }
+    if constexpr (NH >= 2) {
+        hadd_n<C, NREG8, 1>(v);
+        if constexpr (HAS_W) {
+            const double2 e = smT[op.u16_at(38) + 3];
+            const C ee = cmake<C, R>((R)e.x, (R)e.y);
+            v[3] = cmul(v[3], ee);
+            v[7] = cmul(v[7], ee);
+        }
+    }
+    if constexpr (NH >= 3) hadd_n<C, NREG8, 0>(v);
+    const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
+    const uint32_t fl = op.u8_at(34);
+    if (fl & 2u) {  // thread-wide complex factor and / or real scale
+        const double scale = op.m(0);
+        if (fl & 4u) {
+            const uint32_t ts0 = op.tw_tslot(RB), gs0 = op.tw_gslot(RB);
+            const double2 g0 = smE[gs0];
+            const double2 c0 = cmul(make_double2(scale * g0.x, scale * g0.y), cmul(smT[ts0 + c_lo], smT[ts0 + c_hi]));
+            const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
+#pragma unroll
+            for (int j = 0; j < NREG8; ++j) v[j] = cmul(v[j], cc);
+        } else {
+            const R sc = (R)scale;
+#pragma unroll
+            for (int j = 0; j < NREG8; ++j) {
+                v[j].x *= sc;
+                v[j].y *= sc;
+            }
+        }
+    }
+    if (fl & 1u) {
+        if (NH >= 1 || op.tw_abit(2) != 0xFFu) twid8_bit<C, 2>(v, op, smT, smE, c_lo, c_hi);
+        if (NH >= 2 || op.tw_abit(1) != 0xFFu) twid8_bit<C, 1>(v, op, smT, smE, c_lo, c_hi);
+        if (NH >= 3 || op.tw_abit(0) != 0xFFu) twid8_bit<C, 0>(v, op, smT, smE, c_lo, c_hi);
+    }
+}
+
+// thread id -> local index of its register 0: zero bits inserted at the stage's three register positions (ascending)
+__host__ __device__ __forceinline__ uint32_t expand_rb8(uint32_t g, const uint32_t p0, const uint32_t p1, const uint32_t p2) {
+    g = ((g >> p0) << (p0 + 1)) | (g & ((1u << p0) - 1u));
+    g = ((g >> p1) << (p1 + 1)) | (g & ((1u << p1) - 1u));
+    g = ((g >> p2) << (p2 + 1)) | (g & ((1u << p2) - 1u));
+    return g;
+}
+
+// The eight tile slots of a thread from the slot of its register 0 (swizzle and register offsets are XOR-linear).
+__host__ __device__ __forceinline__ void slots8(uint32_t (&a)[NREG8], const uint32_t a0, const uint32_t b0, const uint32_t b1, const uint32_t b2) {
+    a[0] = a0;
+    a[1] = a0 ^ b0;
+    a[2] = a0 ^ b1;
+    a[3] = a[1] ^ b1;
+    a[4] = a0 ^ b2;
+    a[5] = a[1] ^ b2;
+    a[6] = a[2] ^ b2;
+    a[7] = a[3] ^ b2;
+}
+
+// One radix-8 stage on a tile in the TMA layout, first half: shared memory -> 8 registers -> fstage8_math.
+// `a0` = slot of the thread's register 0 = swz128(expand_rb8(tid, rpos...)) (tile independent: the kernel keeps it parked).
+template <typename C, typename R, typename OP>
+__host__ __device__ __forceinline__ void fstage8_compute(const OP& op, const C* tile, const double2* __restrict__ smT,
+                                                         const double2* __restrict__ smE, const uint32_t tid, const uint32_t a0, C (&w)[NREG8]) {
+    uint32_t a[NREG8];
+    slots8(a, a0, op.boff(0), op.boff(1), op.boff(2));
+#pragma unroll
+    for (int j = 0; j < NREG8; ++j) w[j] = tile[a[j]];
+    switch (op.type() - DC_FSTAGE) {  // shape = 2 * (number of butterflies) + (phase tables present)
+        case 0: case 1: fstage8_math<C, R, 0, false>(w, op, smT, smE, tid); break;
+        case 2: fstage8_math<C, R, 1, false>(w, op, smT, smE, tid); break;
+        case 3: fstage8_math<C, R, 1, true>(w, op, smT, smE, tid); break;
+        case 4: fstage8_math<C, R, 2, false>(w, op, smT, smE, tid); break;
+        case 5: fstage8_math<C, R, 2, true>(w, op, smT, smE, tid); break;
+        case 6: fstage8_math<C, R, 3, false>(w, op, smT, smE, tid); break;
+        default: fstage8_math<C, R, 3, true>(w, op, smT, smE, tid); break;
+    }
+}
+// ... second half: the registers go back to shared memory, to the slots they came from (a0, the stage's offsets) or -- last
+// stage of a bit-permuting sweep, after a barrier -- to the slots of the OUTPUT tile order (a0 and offsets of that order).
+template <typename C>
+__host__ __device__ __forceinline__ void fstage8_put(C* tile, const uint32_t a0, const uint32_t b0, const uint32_t b1, const uint32_t b2,
+                                                     const C (&w)[NREG8]) {
+    uint32_t a[NREG8];
+    slots8(a, a0, b0, b1, b2);
+#pragma unroll
+    for (int j = 0; j < NREG8; ++j) tile[a[j]] = w[j];
+}
+
 // One op of the generic interpreter applied to a thread's 16 registers (everything but the stage changes).
 template <typename C, typename R, bool LEAN>
 __host__ __device__ __forceinline__ void generic_op(C (&v)[NREG], const OpR& op, const uint32_t type, const bool tpred,
@@ -508,17 +697,21 @@ _Pragma("unroll") for (int j = 0; j < NREG; ++j) if ((wm >> j) & 1) {  \
 //   IMG_LEAN  the op set of Hadamard/phase circuits only (stage, uncontrolled dense, unnormalised butterfly, phase tables);
 //   IMG_FFT   launches made of OP_FSTAGE ops only: no amplitude is carried in registers from one op to the next, so the
 //             op loop has no register-allocation joins (the generic loop spends ~20 % of its instructions on moves there).
+//   IMG_FFT8  the same shape with three register bits per stage, 256-thread CTAs, TMA tile loads and stores (qsv_sweep8.cu);
+//             chosen per launch when the sweep's targets fit radix-8 stages as well and its tile fits the TMA descriptor.
 #define IMG_FULL 0
 #define IMG_LEAN 1
 #define IMG_FFT 2
+#define IMG_FFT8 3
 
 struct PlanStep {
     bool fused;
     size_t gate_index;      // !fused: index into ctx->gates
     SweepParams* params;    // fused (host copy)
     bool out_of_place;
-    int img;                // kernel image that runs it: IMG_FFT (only OP_FSTAGE ops), IMG_LEAN (lean op set) or IMG_FULL
+    int img;                // kernel image that runs it: IMG_FFT / IMG_FFT8 (only OP_FSTAGE ops), IMG_LEAN (lean op set) or IMG_FULL
     uint64_t n_gates;       // source gates carried
+    Sweep8Extra* tma;       // IMG_FFT8: how the TMA engine sees a tile on load / store (host copy, owned)
 };
 
 struct SweepPlan {
@@ -530,7 +723,10 @@ struct SweepPlan {
     std::vector<cudaEvent_t> ev;  // profiling
     std::vector<float> ms;
     ~SweepPlan() {
-        for (auto& s : steps) delete s.params;
+        for (auto& s : steps) {
+            delete s.params;
+            delete s.tma;
+        }
         if (d_aux) cudaFree(d_aux);
         for (auto e : ev) cudaEventDestroy(e);
     }
