@@ -783,9 +783,26 @@ struct Builder {
         X.loc_perm = make_segmap(rank_of);
         // the last stage's register bit q sits at tile bit p_q (recovered from its slot offset: the swizzle only adds lower bits)
         const SwOp& last = e.ops.back();
+        int p_last[RB8];
         for (int q = 0; q < RB8; ++q) {
-            const int p_q = 31 - __builtin_clz((unsigned)last.fs.boff[q]);
-            X.boff_out[q] = (uint16_t)swz128(1u << rank_of[p_q]);
+            p_last[q] = 31 - __builtin_clz((unsigned)last.fs.boff[q]);
+            X.boff_out[q] = (uint16_t)swz128(1u << rank_of[p_last[q]]);
+        }
+        static const bool no_mid = getenv("QSV_NO_MIDLAYOUT") != nullptr;  // A/B aid
+        if (e.ops.size() == 2 && !no_mid) {
+            // intermediate layout: see Sweep8Extra
+            X.mid_layout = 1;
+            const SwOp& first = e.ops[0];
+            for (int q = 0; q < RB8; ++q) {
+                const int p_first = 31 - __builtin_clz((unsigned)first.fs.boff[q]);
+                X.boff_mid_w[q] = (uint16_t)swz(1u << p_first);
+                X.boff_last_r[q] = (uint16_t)swz(1u << p_last[q]);
+            }
+            std::vector<int> rest;  // the last stage's thread bits: its non-register tile bits, lowest OUTPUT position first
+            for (int l = 0; l < k; ++l)
+                if (l != p_last[0] && l != p_last[1] && l != p_last[2]) rest.push_back(l);
+            std::sort(rest.begin(), rest.end(), [&](int x, int y) { return rank_of[x] < rank_of[y]; });
+            X.tmap_last = make_segmap(rest);
         }
         return true;
     }

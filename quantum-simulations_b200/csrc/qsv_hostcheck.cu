@@ -65,7 +65,37 @@ static int sweep8_emulate_host(qsv_ctx* ctx, const SweepParams& P, const Sweep8E
             smE[gs] = e;
         }
         if (!engine_copy(X.in, seg_apply64x(t, D.in_glob), true, src, nullptr)) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: TMA load box leaves the tensor");
-        for (int i = 0; i < D.n_ops; ++i) {
+        if (X.mid_layout) {
+            // two-stage permuting launch through the intermediate swz() layout: each stage computes everything, then writes
+            if (D.n_ops != 2) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: mid layout with %d ops", D.n_ops);
+            const OpView op0{&P.ops[0]}, op1{&P.ops[1]};
+            for (uint32_t tid = 0; tid < threads; ++tid) {
+                const uint32_t bl = expand_rb8(tid, op0.rpos(0), op0.rpos(1), op0.rpos(2));
+                C w[NREG8];
+                fstage8_compute<C, R>(op0, tile, smT.data(), smE.data(), tid, swz128(bl), op0.boff(0), op0.boff(1), op0.boff(2), w);
+                for (int j = 0; j < NREG8; ++j) regs[(size_t)tid * NREG8 + j] = w[j];
+            }
+            for (uint32_t tid = 0; tid < threads; ++tid) {
+                const uint32_t bl = expand_rb8(tid, op0.rpos(0), op0.rpos(1), op0.rpos(2));
+                C w[NREG8];
+                for (int j = 0; j < NREG8; ++j) w[j] = regs[(size_t)tid * NREG8 + j];
+                fstage8_put<C>(tile, swz(bl), X.boff_mid_w[0], X.boff_mid_w[1], X.boff_mid_w[2], w);
+            }
+            for (uint32_t tid = 0; tid < threads; ++tid) {
+                const uint32_t bl1 = seg_apply(tid, X.tmap_last);
+                C w[NREG8];
+                const uint32_t tid_std = compress_rb8(bl1, op1.rpos(0), op1.rpos(1), op1.rpos(2));
+                fstage8_compute<C, R>(op1, tile, smT.data(), smE.data(), tid_std, swz(bl1), X.boff_last_r[0], X.boff_last_r[1], X.boff_last_r[2], w);
+                for (int j = 0; j < NREG8; ++j) regs[(size_t)tid * NREG8 + j] = w[j];
+            }
+            for (uint32_t tid = 0; tid < threads; ++tid) {
+                const uint32_t bl1 = seg_apply(tid, X.tmap_last);
+                C w[NREG8];
+                for (int j = 0; j < NREG8; ++j) w[j] = regs[(size_t)tid * NREG8 + j];
+                fstage8_put<C>(tile, swz128(seg_apply(bl1, X.loc_perm)), X.boff_out[0], X.boff_out[1], X.boff_out[2], w);
+            }
+        }
+        for (int i = 0; i < D.n_ops && !X.mid_layout; ++i) {
             const OpView op{&P.ops[i]};
             if (op.type() < DC_FSTAGE || op.type() >= DC_FSTAGE + 8) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: op %d of a radix-8 launch is not a radix-8 OP_FSTAGE", i);
             const bool reorder = i == D.n_ops - 1 && X.permuting;
@@ -74,7 +104,7 @@ static int sweep8_emulate_host(qsv_ctx* ctx, const SweepParams& P, const Sweep8E
             for (uint32_t tid = 0; tid < threads; ++tid) {
                 const uint32_t bl = expand_rb8(tid, op.rpos(0), op.rpos(1), op.rpos(2));
                 C w[NREG8];
-                fstage8_compute<C, R>(op, tile, smT.data(), smE.data(), tid, swz128(bl), w);
+                fstage8_compute<C, R>(op, tile, smT.data(), smE.data(), tid, swz128(bl), op.boff(0), op.boff(1), op.boff(2), w);
                 if (!reorder) fstage8_put<C>(tile, swz128(bl), op.boff(0), op.boff(1), op.boff(2), w);
                 else for (int j = 0; j < NREG8; ++j) regs[(size_t)tid * NREG8 + j] = w[j];
             }

@@ -46,6 +46,9 @@ struct Sweep8Params {
     int permuting;            // the last stage re-orders the tile for a bit-permuting store
     SegMap loc_perm;          // input-local index -> output-local index (bit permutation)
     uint16_t boff_out[RB8];   // output-order slot offset of the last stage's register bit q
+    int mid_layout;           // two-stage permuting launch through the intermediate swz() layout (Sweep8Extra)
+    SegMap tmap_last;
+    uint16_t boff_mid_w[RB8], boff_last_r[RB8];
 };
 
 namespace {
@@ -143,8 +146,8 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
     C* const buf0 = reinterpret_cast<C*>(smem_raw);
     double2* const smE0 = reinterpret_cast<double2*>(smem_raw + 2 * tile_bytes);  // [2][MAX_GSLOT8] per-tile scalars by tile parity
     double2* const smT = smE0 + 2 * MAX_GSLOT8;
-    uint32_t* const park = reinterpret_cast<uint32_t*>(smT + MAX_TAB);  // [PARK8_OPS + 1][blockDim]: slot of register 0 per stage / on output
-    uint64_t* const mbar = reinterpret_cast<uint64_t*>(park + (PARK8_OPS + 1) * blockDim.x);
+    uint32_t* const park = reinterpret_cast<uint32_t*>(smT + MAX_TAB);  // [PARK8_WORDS][blockDim]: slot of register 0 per stage, read / write side
+    uint64_t* const mbar = reinterpret_cast<uint64_t*>(park + PARK8_WORDS * blockDim.x);
     const double2* aux2 = reinterpret_cast<const double2*>(aux);
 
     const uint32_t tid = threadIdx.x;
@@ -156,7 +159,15 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
         return expand_rb8(tid, o.rpos(0), o.rpos(1), o.rpos(2));
     };
     for (int i = 0; i < n_ops && i < PARK8_OPS; ++i) park[i * blockDim.x + tid] = swz128(slot0(i));
-    if (P.permuting) park[PARK8_OPS * blockDim.x + tid] = swz128(seg_apply(slot0(n_ops - 1), P.loc_perm));
+    if (P.mid_layout) {  // (two stages) first stage writes swz(), last stage reads swz() with its lanes on the output order's low bits
+        const uint32_t bl1 = seg_apply(tid, P.tmap_last);
+        park[3 * blockDim.x + tid] = swz(slot0(0));
+        const OpView o1{&P.ops[1]};  // (the phase tables of the stage are indexed by the thread number of the standard assignment)
+        park[1 * blockDim.x + tid] = swz(bl1) | (compress_rb8(bl1, o1.rpos(0), o1.rpos(1), o1.rpos(2)) << 16);
+        park[2 * blockDim.x + tid] = swz128(seg_apply(bl1, P.loc_perm));
+    } else if (P.permuting) {
+        park[2 * blockDim.x + tid] = swz128(seg_apply(slot0(n_ops - 1), P.loc_perm));
+    }
     for (uint32_t i = tid; i < D.tab_len; i += blockDim.x) smT[i] = aux2[D.tab_off + i];
     if (tid == 0) {
         if (smem_u32(smem_raw) & 1023u) __trap();  // the 128-byte swizzle pattern is anchored at 1 KB
@@ -221,18 +232,31 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
         } else if (more && tid >= blockDim.x - (uint32_t)D.n_gslots) {
             scalars(tn, smE0 + (cur ^ 1) * MAX_GSLOT8, blockDim.x - 1 - tid);
         }
-        for (int i = 0; i < n_ops; ++i) {
-            const OpView op{&P.ops[i]};
-            const uint32_t a0 = i < PARK8_OPS ? park[i * blockDim.x + tid] : swz128(slot0(i));
+        if (P.mid_layout) {
             C w[NREG8];
-            fstage8_compute<C, R>(op, tile, smT, smE, tid, a0, w);
-            if (i == n_ops - 1 && P.permuting) {
-                __syncthreads();  // the output order uses other threads' slots: everyone has read first
-                fstage8_put<C>(tile, park[PARK8_OPS * blockDim.x + tid], P.boff_out[0], P.boff_out[1], P.boff_out[2], w);
-            } else {
-                fstage8_put<C>(tile, a0, op.boff(0), op.boff(1), op.boff(2), w);
+            const OpView op0{&P.ops[0]}, op1{&P.ops[1]};
+            fstage8_compute<C, R>(op0, tile, smT, smE, tid, park[tid], op0.boff(0), op0.boff(1), op0.boff(2), w);
+            __syncthreads();  // (each stage of this mode writes other threads' slots: everyone reads first)
+            fstage8_put<C>(tile, park[3 * blockDim.x + tid], P.boff_mid_w[0], P.boff_mid_w[1], P.boff_mid_w[2], w);
+            __syncthreads();
+            const uint32_t pk = park[blockDim.x + tid];
+            fstage8_compute<C, R>(op1, tile, smT, smE, pk >> 16, pk & 0xFFFFu, P.boff_last_r[0], P.boff_last_r[1], P.boff_last_r[2], w);
+            __syncthreads();
+            fstage8_put<C>(tile, park[2 * blockDim.x + tid], P.boff_out[0], P.boff_out[1], P.boff_out[2], w);
+        } else {
+            for (int i = 0; i < n_ops; ++i) {
+                const OpView op{&P.ops[i]};
+                const uint32_t a0 = i < PARK8_OPS ? park[i * blockDim.x + tid] : swz128(slot0(i));
+                C w[NREG8];
+                fstage8_compute<C, R>(op, tile, smT, smE, tid, a0, op.boff(0), op.boff(1), op.boff(2), w);
+                if (i == n_ops - 1 && P.permuting) {
+                    __syncthreads();  // the output order uses other threads' slots: everyone has read first
+                    fstage8_put<C>(tile, park[2 * blockDim.x + tid], P.boff_out[0], P.boff_out[1], P.boff_out[2], w);
+                } else {
+                    fstage8_put<C>(tile, a0, op.boff(0), op.boff(1), op.boff(2), w);
+                }
+                if (i < n_ops - 1) __syncthreads();
             }
-            if (i < n_ops - 1) __syncthreads();
         }
         fence_async_smem();  // this thread's tile writes are visible to the engine once it has passed the next barrier
     }
@@ -309,7 +333,13 @@ int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const 
     fill_coords(P->out, X.out);
     P->permuting = X.permuting;
     P->loc_perm = X.loc_perm;
-    for (int q = 0; q < RB8; ++q) P->boff_out[q] = X.boff_out[q];
+    P->mid_layout = X.mid_layout;
+    P->tmap_last = X.tmap_last;
+    for (int q = 0; q < RB8; ++q) {
+        P->boff_out[q] = X.boff_out[q];
+        P->boff_mid_w[q] = X.boff_mid_w[q];
+        P->boff_last_r[q] = X.boff_last_r[q];
+    }
     CUtensorMap tm_in, tm_out;
     int rc = encode_tile_map(ctx, X.in, const_cast<void*>(src), &tm_in);
     if (!rc) rc = encode_tile_map(ctx, X.out, dst, &tm_out);

@@ -23,9 +23,10 @@
 #define MAX_OPS8 8       // stages per launch (an FFT-shaped launch is one op per stage)
 #define MAX_GSLOT8 16    // per-tile phase scalars per launch of the radix-8 image
 #define PARK8_OPS 2      // stages whose per-thread slot constants are parked in shared memory (later ones recompute them)
+#define PARK8_WORDS 4    // + the write-side constants of a permuting launch: [2] last stage (output order), [3] first stage (mid layout)
 #define TMA_MAX_INST 16  // cp.async.bulk.tensor instructions per tile when the tile's bit runs need more than 5 dimensions
 #define SWEEP8_SMEM(k, threads) \
-    (2 * ((size_t)16 << (k)) + (2 * MAX_GSLOT8 + MAX_TAB) * sizeof(double2) + (size_t)(threads) * 4 * (PARK8_OPS + 1) + 32)
+    (2 * ((size_t)16 << (k)) + (2 * MAX_GSLOT8 + MAX_TAB) * sizeof(double2) + (size_t)(threads) * 4 * PARK8_WORDS + 32)
 
 enum : uint8_t { OP_STAGE = 0, OP_DENSE = 1, OP_PERMX = 2, OP_MPHASE = 3, OP_W = 4, OP_TWID = 5, OP_HADD = 6, OP_HW = 7, OP_FSTAGE = 8 };
 // Dispatch codes (SwOp::type as stored): the host resolves op kind, target register bit, real/complex
@@ -171,11 +172,23 @@ struct TmaTile {
 // bit-permuting sweep: the tile goes out in the order of its OUTPUT positions) and, for the permuting case, how the last
 // stage re-orders the tile in shared memory -- input-local index -> output-local index is a bit permutation (loc_perm), so
 // the output slots keep the XOR structure: slot of register 0 plus one offset per register bit (boff_out).
+//
+// A plain re-ordering store would leave the lanes spread over the INPUT order's low bits, i.e. over high bits of the output
+// order: an 8-way bank conflict on every store (measured: 8.5 ms for the permuting QFT-30 sweep against 5.9 ms for the
+// others).  Two-stage launches therefore pass through an intermediate layout (mid_layout): the first stage writes the tile
+// back in input order but in swz() -- which folds tile bits 3..11 into the bank bits, not only 3..5 -- and the last stage
+// assigns its threads so that the lanes walk the bits that are LOW in the output order (tmap_last).  Its loads are then
+// conflict-free in swz() and its stores conflict-free in the engine's swizzle of the output order; each stage reads
+// everything before it writes (one more barrier).
 struct Sweep8Extra {
     TmaTile in, out;
     int permuting;
     SegMap loc_perm;
     uint16_t boff_out[RB8];
+    int mid_layout;
+    SegMap tmap_last;             // thread id -> input-local index of its register 0 in the last stage
+    uint16_t boff_mid_w[RB8];     // swz() slot offset of the first stage's register bit q (its write side)
+    uint16_t boff_last_r[RB8];    // swz() slot offset of the last stage's register bit q (its read side)
 };
 
 // An op held in registers: header words + 64-byte payload (all accesses statically indexed).
@@ -594,6 +607,14 @@ __host__ __device__ __forceinline__ uint32_t expand_rb8(uint32_t g, const uint32
     return g;
 }
 
+// ... and back: the thread number the planner's thread-phase tables assume for a register-0 index (positions descending)
+__host__ __device__ __forceinline__ uint32_t compress_rb8(uint32_t g, const uint32_t p0, const uint32_t p1, const uint32_t p2) {
+    g = ((g >> (p2 + 1)) << p2) | (g & ((1u << p2) - 1u));
+    g = ((g >> (p1 + 1)) << p1) | (g & ((1u << p1) - 1u));
+    g = ((g >> (p0 + 1)) << p0) | (g & ((1u << p0) - 1u));
+    return g;
+}
+
 // The eight tile slots of a thread from the slot of its register 0 (swizzle and register offsets are XOR-linear).
 __host__ __device__ __forceinline__ void slots8(uint32_t (&a)[NREG8], const uint32_t a0, const uint32_t b0, const uint32_t b1, const uint32_t b2) {
     a[0] = a0;
@@ -610,9 +631,10 @@ __host__ __device__ __forceinline__ void slots8(uint32_t (&a)[NREG8], const uint
 // `a0` = slot of the thread's register 0 = swz128(expand_rb8(tid, rpos...)) (tile independent: the kernel keeps it parked).
 template <typename C, typename R, typename OP>
 __host__ __device__ __forceinline__ void fstage8_compute(const OP& op, const C* tile, const double2* __restrict__ smT,
-                                                         const double2* __restrict__ smE, const uint32_t tid, const uint32_t a0, C (&w)[NREG8]) {
+                                                         const double2* __restrict__ smE, const uint32_t tid, const uint32_t a0,
+                                                         const uint32_t b0, const uint32_t b1, const uint32_t b2, C (&w)[NREG8]) {
     uint32_t a[NREG8];
-    slots8(a, a0, op.boff(0), op.boff(1), op.boff(2));
+    slots8(a, a0, b0, b1, b2);
 #pragma unroll
     for (int j = 0; j < NREG8; ++j) w[j] = tile[a[j]];
     switch (op.type() - DC_FSTAGE) {  // shape = 2 * (number of butterflies) + (phase tables present)
