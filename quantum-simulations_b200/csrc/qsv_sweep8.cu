@@ -46,6 +46,7 @@ struct Sweep8Params {
     int permuting;            // the last stage re-orders the tile for a bit-permuting store
     SegMap loc_perm;          // input-local index -> output-local index (bit permutation)
     uint16_t boff_out[RB8];   // output-order slot offset of the last stage's register bit q
+    int l2_prefetch;          // tiles ahead of the load proper that are prefetched into L2 (0 = off)
     int mid_layout;           // two-stage permuting launch through the intermediate swz() layout (Sweep8Extra)
     SegMap tmap_last;
     uint16_t boff_mid_w[RB8], boff_last_r[RB8];
@@ -106,6 +107,21 @@ __device__ __forceinline__ void tma_load(const CUtensorMap* tm, void* smem_dst, 
                 "cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];" ::"r"(d),
                 "l"(m), "r"(b), "r"(0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
                 : "memory");
+            break;
+    }
+}
+// one box: global -> L2 only (no shared-memory buffer is needed yet: issued a tile earlier than the load proper)
+__device__ __forceinline__ void tma_prefetch_l2(const CUtensorMap* tm, int rank, int c1, int c2, int c3, int c4) {
+    const uint64_t m = reinterpret_cast<uint64_t>(tm);
+    switch (rank) {
+        case 2: asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(m), "r"(0), "r"(c1) : "memory"); break;
+        case 3: asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(m), "r"(0), "r"(c1), "r"(c2) : "memory"); break;
+        case 4:
+            asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];" ::"l"(m), "r"(0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+            break;
+        default:
+            asm volatile("cp.async.bulk.prefetch.tensor.5d.L2.global.tile [%0, {%1, %2, %3, %4, %5}];" ::"l"(m), "r"(0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+                         : "memory");
             break;
     }
 }
@@ -202,6 +218,14 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
             tma_load(&tm_in, smem_raw + (size_t)b * tile_bytes + (size_t)e * P.in.inst_amps * sizeof(C), &mbar[b], P.in.rank, c1, c2, c3, c4);
         }
     };
+    auto issue_prefetch = [&](uint32_t t) {  // one thread
+        const uint64_t phys = seg_apply64x(t, D.in_glob);
+        for (int e = 0; e < P.in.n_inst; ++e) {
+            int c1, c2, c3, c4;
+            box_coords(P.in, phys | P.in.inst_goff[e], c1, c2, c3, c4);
+            tma_prefetch_l2(&tm_in, P.in.rank, c1, c2, c3, c4);
+        }
+    };
     auto issue_store = [&](uint32_t t, int b) {  // one thread; the tile in buffer b is complete and fenced
         const uint64_t phys = seg_apply64x(t, D.out_glob);
         for (int e = 0; e < P.out.n_inst; ++e) {
@@ -229,6 +253,10 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
                 asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             }
             if (more) issue_load(tn, cur ^ 1);
+            if (P.l2_prefetch) {
+                const uint64_t tp = (uint64_t)t + (uint64_t)(1 + P.l2_prefetch) * grid_x8();
+                if (tp < n_tiles) issue_prefetch((uint32_t)tp);
+            }
         } else if (more && tid >= blockDim.x - (uint32_t)D.n_gslots) {
             scalars(tn, smE0 + (cur ^ 1) * MAX_GSLOT8, blockDim.x - 1 - tid);
         }
@@ -333,6 +361,8 @@ int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const 
     fill_coords(P->out, X.out);
     P->permuting = X.permuting;
     P->loc_perm = X.loc_perm;
+    static const int l2pf = getenv("QSV_L2_PREFETCH") ? atoi(getenv("QSV_L2_PREFETCH")) : 0;  // A/B aid: measured slower, see profiles/r2_ab_sweep8.txt
+    P->l2_prefetch = l2pf;
     P->mid_layout = X.mid_layout;
     P->tmap_last = X.tmap_last;
     for (int q = 0; q < RB8; ++q) {
