@@ -134,6 +134,11 @@ int qsv_fuse(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps);
  * (tests/qompiler/circuits/test_qompiler.py:79-82).                                 */
 int qsv_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, void* stream);
 
+/* Shape of the fused plan built by qsv_fuse: number of fused sweeps and how many of them store out of place (each of
+ * those makes qsv_run's result change buffers once).  Ranks of a sharded run use it to agree, before the first run, on
+ * which of their two buffers will hold a segment's result.  No reference counterpart.                          */
+int qsv_plan_info(qsv_ctx* ctx, uint64_t* out_sweeps, uint64_t* out_of_place_sweeps);
+
 /* Profiling: when on, every fused sweep launched by qsv_run is bracketed by CUDA events on the
  * launch stream; qsv_get_sweep_profile waits for them and returns their durations in launch
  * order (*n_out = how many were recorded, at most `cap` are written).  No reference

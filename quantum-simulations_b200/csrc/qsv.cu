@@ -738,6 +738,17 @@ int qsv_fuse(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
     return sweep_plan_build(ctx, max_tile_bits, out_sweeps);
 }
 
+int qsv_plan_info(qsv_ctx* ctx, uint64_t* out_sweeps, uint64_t* out_of_place_sweeps) {
+    if (!ctx) return QSV_E_INVALID;
+    uint64_t s = 0, o = 0;
+    if (ctx->rows_plan) s = 1;
+    else if (ctx->plan) sweep_plan_count(ctx->plan, &s, &o);
+    else return qsv_fail(ctx, QSV_E_NOPROGRAM, "qsv_plan_info before qsv_fuse");
+    if (out_sweeps) *out_sweeps = s;
+    if (out_of_place_sweeps) *out_of_place_sweeps = o;
+    return QSV_OK;
+}
+
 int qsv_set_profiling(qsv_ctx* ctx, int on) {
     if (!ctx) return QSV_E_INVALID;
     ctx->profile = on != 0;

@@ -96,6 +96,7 @@ void sweep_plan_free(SweepPlan* p);
 int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps);
 int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream);
 int sweep_plan_collect_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out);
+void sweep_plan_count(const SweepPlan* plan, uint64_t* sweeps, uint64_t* out_of_place);
 // implemented in qsv_rows.cu
 void rowslab_free(RowSlabPlan* p);
 int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out);

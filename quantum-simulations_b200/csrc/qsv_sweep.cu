@@ -256,6 +256,15 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
 // host: plan upload, launch, run (the fusion pass itself is in qsv_fuse.cu)
 // ================================================================================================
 void sweep_plan_free(SweepPlan* p) { delete p; }
+void sweep_plan_count(const SweepPlan* plan, uint64_t* sweeps, uint64_t* out_of_place) {
+    uint64_t s = 0, o = 0;
+    for (auto& st : plan->steps) {
+        s += st.fused;
+        o += st.fused && st.out_of_place;
+    }
+    *sweeps = s;
+    *out_of_place = o;
+}
 
 
 static int sweep_set_smem_attr(qsv_ctx* ctx, int k);

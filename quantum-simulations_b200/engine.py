@@ -111,6 +111,12 @@ class Engine:
         check(self.lib.qsv_fuse(self._ctx, max_tile_bits, C.byref(n)), self._ctx)
         return int(n.value)
 
+    def plan_info(self):
+        """(fused sweeps, out-of-place sweeps) of the plan built by :meth:`fuse`."""
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        check(self.lib.qsv_plan_info(self._ctx, C.byref(a), C.byref(b)), self._ctx)
+        return int(a.value), int(b.value)
+
     def run(self, state, spare=None):
         """Apply the uploaded program; returns the tensor that holds the result."""
         flag = C.c_int(0)

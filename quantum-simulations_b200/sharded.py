@@ -394,31 +394,44 @@ class GpuExecutor:
         self.engines = {}
         self.launches = 0
         self.fused_sweeps_per_apply = 0   # fused compute sweeps of all prepared segments together (one apply runs each once)
+        self.copy_back = {}               # segment key -> True: this rank copies the result back to the buffer it started in
 
     def prepare(self, key, recs, pool, n_loc):
         from .engine import Engine
         eng = Engine(self.device, np.complex128)
         eng.upload_records(recs, pool, n_loc, 0)
         fused = False
+        flips = 0
         if self.fuse and len(recs):
             # (no per-gate downgrade here: a segment the fusion pass refuses is a planning error at these sizes)
             self.fused_sweeps_per_apply += int(eng.fuse(self.tile_bits))
             fused = True
+            flips = eng.plan_info()[1] & 1
         self.engines[key] = (eng, fused)
+        return flips
+
+    def agree_on_buffers(self, keys, flips, all_reduce_min):
+        """A segment's result lands in the other buffer when its plan has an odd number of out-of-place sweeps, and the
+        plans are per rank: a rank whose global control is not satisfied drops gates the others keep (their SWAP
+        relabels with them).  The fused exchange stores into EVERY rank's spare buffer, so all ranks must agree on
+        which one that is.  ``all_reduce_min`` reduces an int list over the ranks; where the ranks disagree, the odd
+        ones copy their result back (one extra pass on those ranks only) so that every rank ends where it started."""
+        agreed = all_reduce_min(list(flips))
+        for key, mine, low in zip(keys, flips, agreed):
+            self.copy_back[key] = bool(mine and not low)
 
     def run_segment(self, key, state, spare):
         eng, fused = self.engines[key]
         res = eng.run(state, spare if fused else None)
+        if res is not state and self.copy_back.get(key):
+            state.copy_(res)
+            return state, spare
         return (res, state) if res is not state else (state, spare)
 
     def permute(self, state, spare, n_loc, perm):
         import ctypes as C
         from ._lib import check
-        eng = next(iter(self.engines.values()))[0] if self.engines else None
-        if eng is None:
-            from .engine import Engine
-            eng = Engine(self.device, np.complex128)
-            self.engines["_perm"] = (eng, False)
+        eng = self.any_engine()
         p = np.ascontiguousarray(perm, dtype=np.int32)
         check(eng.lib.qsv_permute_bits(eng._ctx, C.c_void_p(state.data_ptr()), C.c_void_p(spare.data_ptr()), n_loc,
                                        p.ctypes.data_as(C.c_void_p), eng._stream()), eng._ctx)
@@ -443,24 +456,32 @@ class GpuExecutor:
 
 
 class ShardedCircuit:
-    """A planned, rank-localised circuit ready to be applied repeatedly to this rank's shard."""
+    """A planned, rank-localised circuit ready to be applied repeatedly to this rank's shard.
 
-    def __init__(self, recs, pool, n_bits, rank, world, executor, exchanger, restore=True):
+    ``restore=False`` leaves the result in the layout the last segment ended in and reports it as
+    ``final_where`` (logical bit -> physical position, global positions last): QFT then needs two exchange steps
+    instead of three -- its final SWAP layer becomes output ordering."""
+
+    def __init__(self, recs, pool, n_bits, rank, world, executor, exchanger, restore=True, all_reduce_min=None):
         g = world.bit_length() - 1
         assert 1 << g == world, "world size must be a power of two"
         self.plan = plan_sharded(recs, n_bits, g, restore=restore)
+        self.final_where = list(self.plan.final_where)
         self.rank, self.world = rank, world
         self.executor, self.exchanger = executor, exchanger
         self.n_loc = self.plan.n_loc
         self.n_gates = len(recs)
         li = 0
         self._keys = []
+        flips = []
         for s in self.plan.steps:
             if s[0] == "local":
                 lrecs, lpool = localize_records(recs, pool, s[1], self.plan.where_at[li], self.n_loc, rank)
-                executor.prepare(li, lrecs, lpool, self.n_loc)
+                flips.append(int(executor.prepare(li, lrecs, lpool, self.n_loc) or 0))
                 self._keys.append(li)
                 li += 1
+        if all_reduce_min is not None and hasattr(executor, "agree_on_buffers"):
+            executor.agree_on_buffers(self._keys, flips, all_reduce_min)
 
     def apply(self, state, spare, timers=None):
         """Returns (state, spare) -- the buffers may have traded places.  ``timers`` (a list) collects one
@@ -505,19 +526,11 @@ class ShardedCircuit:
 # ---------------------------------------------------------------------------------------------
 # benchmark entry (bench.py --gpus N under torchrun)
 # ---------------------------------------------------------------------------------------------
-def bench_main(args):
+def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
+    """One sharded workload (QFT-n over `world` GPUs): timed steps, per-step-kind split, self-check, e2e.  Every rank
+    runs it; the returned record is complete on rank 0."""
     import torch
     import torch.distributed as dist
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world == 1:
-        raise SystemExit("bench.py --gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
-    torch.cuda.set_device(local_rank)
-    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
-    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-    import bench as B
-    n = args.qubits or 30
     g = world.bit_length() - 1
     prog, recs, pool = B.qft_records(n)
     n_loc = n - g
@@ -561,8 +574,15 @@ def bench_main(args):
     execu = GpuExecutor(local_rank, fuse=not args.no_fuse, tile_bits=args.tile_bits)
     if exch is None:
         exch = TorchExchanger(rank, world)
-    circ = ShardedCircuit(recs, pool, n, rank, world, execu, exch)
-    for _ in range(args.warmup):
+
+    def all_reduce_min(values):
+        t = torch.tensor(values if values else [0], device=dev, dtype=torch.int32)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return [int(v) for v in t.tolist()][:len(values)]
+
+    restore = bool(getattr(args, "restore_layout", False))
+    circ = ShardedCircuit(recs, pool, n, rank, world, execu, exch, restore=restore, all_reduce_min=all_reduce_min)
+    for _ in range(warmup):
         state, spare = circ.apply(state, spare)
     torch.cuda.synchronize()
     dist.barrier()
@@ -574,7 +594,7 @@ def bench_main(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         state, spare = circ.apply(state, spare)
     e1.record()
     torch.cuda.synchronize()
@@ -597,35 +617,89 @@ def bench_main(args):
     sp_t = torch.tensor([split.get("local", 0.0), split.get("permute", 0.0), split.get("xall", 0.0) + split.get("exchange", 0.0)],
                         device=dev, dtype=torch.float64)
     dist.all_reduce(sp_t, op=dist.ReduceOp.MAX)
-    # norm check (unitarity) as a cheap correctness guard of the whole sharded run
-    nrm = torch.linalg.vector_norm(state) ** 2
-    dist.all_reduce(nrm)
-    # end to end through host buffers: every rank uploads its shard from pinned memory, applies the circuit and
-    # downloads the result, every step; max over ranks
+    # ---- correctness at this size, outside the timed region: QFT of a basis state against the closed form on every
+    # amplitude of every shard (the layout the run ends in is read through the plan's bit-position table), plus the norm
+    check = None
+    if not getattr(args, "no_check", False) and B.workload_kind() == "qft":
+        x0 = B.CHECK_X & ((1 << n) - 1)
+        state.zero_()
+        if (x0 >> n_loc) == rank:
+            state[x0 & (amps - 1)] = 1.0
+        dist.barrier()
+        state, spare = circ.apply(state, spare)
+        torch.cuda.synchronize()
+        err = B.qft_basis_error(state, n, x0, base_index=rank << n_loc, where=circ.final_where)
+        nrm2 = torch.linalg.vector_norm(state) ** 2
+        both = torch.tensor([err], device=dev, dtype=torch.float64)
+        dist.all_reduce(both, op=dist.ReduceOp.MAX)
+        dist.all_reduce(nrm2)
+        err = float(both.item())
+        check = {"tolerance": 1e-10, "check": f"QFT|x0={x0:#x}> against the closed form on all 2^{n} amplitudes (every rank its shard, max over ranks); norm",
+                 "max_abs_err": err, "max_rel_err": err * 2.0 ** (n / 2), "norm_after": float(nrm2.item()),
+                 "layout": "canonical" if circ.final_where == list(range(n)) else "permuted: read through the plan's bit-position table",
+                 "ok": bool(err <= 1e-10 and err * 2.0 ** (n / 2) <= 1e-9 and abs(float(nrm2.item()) - 1) <= 1e-9)}
+    # ---- end to end through host buffers: every rank uploads its shard from pinned memory, applies the circuit and
+    # downloads the result, every step.  Steps are independent jobs: the upload of step i+1 and the download of step
+    # i-1 run on their own streams (staging buffers on the device) under the compute of step i; max over ranks
     e2e = None
-    if args.e2e_steps > 0:
-        host = torch.empty(amps, dtype=torch.complex128, pin_memory=True)
-        host.copy_(state)
+    if e2e_steps > 0:
+        host_in = torch.empty(amps, dtype=torch.complex128, pin_memory=True)
+        host_out = torch.empty(amps, dtype=torch.complex128, pin_memory=True)
+        host_in.copy_(state)
+        stage_in = torch.empty(amps, dtype=torch.complex128, device=dev)
+        stage_out = torch.empty(amps, dtype=torch.complex128, device=dev)
+        s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        main = torch.cuda.current_stream()
         torch.cuda.synchronize()
         dist.barrier()
-        t_e2e = []
-        for i in range(args.e2e_steps + 1):
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            dist.barrier()
-            a0.record()
-            state.copy_(host, non_blocking=True)
-            state, spare = circ.apply(state, spare)
-            host.copy_(state, non_blocking=True)
-            a1.record()
-            torch.cuda.synchronize()
-            tt = torch.tensor([a0.elapsed_time(a1)], device=dev, dtype=torch.float64)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            if i > 0:
-                t_e2e.append(float(tt.item()))
-        e2e_ms = float(np.mean(t_e2e))
+
+        def e2e_run(count):
+            nonlocal state, spare
+            ev_in = ev_taken = ev_out = None
+            for i in range(count + 1):
+                if i > 0:          # step i-1: its upload has landed in the staging buffer -> state
+                    main.wait_event(ev_in)
+                    state.copy_(stage_in, non_blocking=True)
+                    ev_taken = torch.cuda.Event()
+                    ev_taken.record(main)
+                if i < count:      # upload of step i, under the compute of step i-1
+                    with torch.cuda.stream(s_in):
+                        if ev_taken is not None:
+                            s_in.wait_event(ev_taken)
+                        stage_in.copy_(host_in, non_blocking=True)
+                        ev_in = torch.cuda.Event()
+                        ev_in.record(s_in)
+                if i > 0:
+                    state, spare = circ.apply(state, spare)
+                    if ev_out is not None:
+                        main.wait_event(ev_out)                # the previous download has left the staging buffer
+                    stage_out.copy_(state, non_blocking=True)
+                    ev_res = torch.cuda.Event()
+                    ev_res.record(main)
+                    with torch.cuda.stream(s_out):
+                        s_out.wait_event(ev_res)
+                        host_out.copy_(stage_out, non_blocking=True)
+                        ev_out = torch.cuda.Event()
+                        ev_out.record(s_out)
+            main.wait_stream(s_out)
+
+        e2e_run(1)
+        torch.cuda.synchronize()
+        dist.barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        s_in.wait_event(a0)
+        e2e_run(e2e_steps)
+        a1.record()
+        torch.cuda.synchronize()
+        tt = torch.tensor([a0.elapsed_time(a1) / e2e_steps], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_ms = float(tt.item())
         e2e = {"value": circ.n_gates / (e2e_ms / 1e3), "unit": "gates/s", "h2d_bytes_per_step": amps * 16 * world,
-               "d2h_bytes_per_step": amps * 16 * world, "ms_per_step": e2e_ms, "steps": args.e2e_steps}
-        del host
+               "d2h_bytes_per_step": amps * 16 * world, "ms_per_step": e2e_ms, "steps": e2e_steps,
+               "note": "per rank: upload of step i+1 and download of step i-1 on their own streams under the compute of step i"}
+        del host_in, host_out, stage_in, stage_out
+    rec = None
     if rank == 0:
         sec = ms / 1e3
         peak, peak_src = B.measured_peak()
@@ -637,28 +711,67 @@ def bench_main(args):
         n_loc_sweeps = int(getattr(execu, "fused_sweeps_per_apply", 0))
         if n_loc_sweeps and float(sp_t[0]) > 0:
             ach = n_loc_sweeps * 2 * amps * 16 / (float(sp_t[0]) * 1e-3) / 1e9
-            local_roof = {"bound": "hbm", "kernel": "k_sweep, local compute sweeps of one step", "sweeps_per_step": n_loc_sweeps,
+            local_roof = {"bound": "hbm", "kernel": "k_sweep8 / k_sweep, local compute sweeps of one step", "sweeps_per_step": n_loc_sweeps,
                           "ms_per_step": float(sp_t[0]), "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                           "frac_of_nominal_8TBps": ach / 8000.0}
-        line = {"metric": "gates_per_sec", "value": args.steps * circ.n_gates / sec, "unit": "gates/s", "n_gpus": world,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": "c128", "data": "synthetic",
-                "config": {"workload": f"qft{n}_statevector_c128", "qubits": n, "amplitudes": 1 << n, "gates": circ.n_gates,
-                           "sharding": f"top {g} qubits over {world} GPUs", "exchanges_per_step": n_ex, "exchange": exch_kind,
-                           "local_amplitudes": amps, "l2": "local shard far larger than the 126 MB L2" if amps * 16 > (1 << 28) else "local shard fits L2"},
-                "amp_GBps": amp_gbps, "hbm_frac_of_measured": amp_gbps / (peak * world),
-                "hbm_frac_of_nominal_8TBps": amp_gbps / (8000.0 * world),
-                "roofline": {"bound": "hbm", "kernel": "k_sweep (fused tile sweep), aggregate over ranks incl. exchange time",
-                             "achieved": amp_gbps / world, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                             "frac": amp_gbps / world / peak, "traffic": None},
-                "local_sweep_roofline": local_roof,
-                "nvlink": {"bytes_sent_per_rank_per_step": float(tot[2]) / world / args.steps, "exchanges_per_step": n_ex,
-                           "exchange_ms_per_step": float(sp_t[2]),
-                           "achieved_GBps_per_direction_per_gpu": (float(tot[2]) / world / args.steps) / (float(sp_t[2]) * 1e-3) / 1e9 if float(sp_t[2]) > 0 else None,
-                           "peak_GBps": 770.0, "peak_source": "measured peer copy per direction (B200_PROFILING.md); nominal 900",
-                           "frac": ((float(tot[2]) / world / args.steps) / (float(sp_t[2]) * 1e-3) / 1e9 / 770.0) if float(sp_t[2]) > 0 else None},
-                "ms_split_one_step": {"local_sweeps": float(sp_t[0]), "local_permutes": float(sp_t[1]), "exchanges": float(sp_t[2])},
-                "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(tot[1]), "clocks": clocks,
-                "norm_after": float(nrm.item())}
+        x_ms = float(sp_t[2])
+        sent = float(tot[2]) / world / max(1, steps)
+        rec = {"metric": "gates_per_sec", "value": steps * circ.n_gates / sec, "unit": "gates/s", "n_gpus": world,
+               "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True,
+               "scaling": "strong", "vs_baseline": None, "dtype": "c128", "data": "synthetic",
+               "config": B.workload_config(n, circ.n_gates),
+               "impl_config": {"sharding": f"top {g} qubits over {world} GPUs", "exchanges_per_step": n_ex, "exchange": exch_kind,
+                               "local_amplitudes": amps, "restore_layout": restore, "final_bit_positions": circ.final_where,
+                               "l2": "local shard far larger than the 126 MB L2" if amps * 16 > (1 << 28) else "local shard fits L2"},
+               "amp_GBps": amp_gbps, "hbm_frac_of_measured": amp_gbps / (peak * world),
+               "hbm_frac_of_nominal_8TBps": amp_gbps / (8000.0 * world),
+               "roofline": {"bound": "hbm", "kernel": "fused tile sweeps, aggregate over ranks incl. exchange time",
+                            "achieved": amp_gbps / world, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                            "frac": amp_gbps / world / peak, "traffic": None, "traffic_source": None},
+               "local_sweep_roofline": local_roof,
+               "nvlink": {"bytes_sent_per_rank_per_step": sent, "exchanges_per_step": n_ex, "exchange_ms_per_step": x_ms,
+                          "achieved_GBps_per_direction_per_gpu": sent / (x_ms * 1e-3) / 1e9 if x_ms > 0 else None,
+                          "peak_GBps": 770.0, "peak_source": "measured peer copy per direction (B200_PROFILING.md); nominal 900",
+                          "frac": (sent / (x_ms * 1e-3) / 1e9 / 770.0) if x_ms > 0 else None},
+               "ms_split_one_step": {"local_sweeps": float(sp_t[0]), "local_permutes": float(sp_t[1]), "exchanges": x_ms},
+               "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(tot[1]), "clocks": clocks,
+               "check": check, "max_abs_err": check["max_abs_err"] if check else None}
+    del state, spare, circ, execu, exch
+    torch.cuda.empty_cache()
+    return rec, (check is None or check["ok"])
+
+
+def bench_main(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1:
+        raise SystemExit("bench.py --gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench as B
+    if B.workload_kind() != "qft":
+        raise SystemExit("the sharded bench runs the QFT workload (--circuit qft)")
+    n = args.qubits or 30
+    line, ok = _run_sharded(B, args, n, args.steps, args.warmup, args.e2e_steps, rank, world, local_rank)
+    # BASELINE config 5 rides along on 8 GPUs: QFT-34 complex128 (256 GiB state, 32 GiB per GPU) on the same line
+    if world == 8 and not args.qubits and not getattr(args, "no_qft34", False):
+        dist.barrier()
+        sub, ok34 = _run_sharded(B, args, 34, min(args.steps, 3), 1, 0, rank, world, local_rank)
+        ok = ok and ok34
+        if rank == 0:
+            keep = ("value", "unit", "steps", "warmup", "ms_per_step", "config", "impl_config", "amp_GBps", "hbm_frac_of_measured",
+                    "local_sweep_roofline", "nvlink", "ms_split_one_step", "check", "max_abs_err", "gpu_launches")
+            line["qft34"] = {k: sub[k] for k in keep}
+    flag = torch.tensor([1 if ok else 0], device=f"cuda:{local_rank}")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
         print(json.dumps(line))
+        if not int(flag.item()):
+            print(f"[bench] SELF-CHECK FAILED: {line.get('check')} {line.get('qft34', {}).get('check')}", file=sys.stderr)
     dist.destroy_process_group()
+    if not int(flag.item()):
+        sys.exit(3)

@@ -71,7 +71,7 @@ class FakeWorld:
         self.shards[:] = new
 
 
-def run_emulated(recs, pool, n, world, x):
+def run_emulated(recs, pool, n, world, x, restore=True):
     g = world.bit_length() - 1
     n_loc = n - g
     shards = [x[r << n_loc:(r + 1) << n_loc].copy() for r in range(world)]
@@ -85,7 +85,7 @@ def run_emulated(recs, pool, n, world, x):
         def exchange_all(self, state, spare):
             return state, spare
 
-    circs = [ShardedCircuit(recs, pool, n, r, world, OracleExecutor(), NullEx()) for r in range(world)]
+    circs = [ShardedCircuit(recs, pool, n, r, world, OracleExecutor(), NullEx(), restore=restore) for r in range(world)]
     plan = circs[0].plan
     assert all(c.plan.steps == plan.steps for c in circs), "plan must be rank independent"
     li = 0
@@ -113,6 +113,25 @@ def test_qft_sharded_emulation(world):
     assert np.abs(got - orc.qft_reference(x)).max() < 1e-12
     assert plan.final_where == list(range(n))          # canonical layout restored
     assert plan.n_exchanges >= world.bit_length() - 1   # every global H needs its qubit local once
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_qft_sharded_without_layout_restore(world):
+    """restore=False: two exchange steps instead of three; the result is the FFT of the input read through the plan's
+    bit-position table (logical bit b at physical position final_where[b]) -- QFT's SWAP layer became output ordering."""
+    n = 10
+    prog = qft_program(n)
+    x = random_state(1 << n)
+    got, plan = run_emulated(prog.records(), prog.pool(), n, world, x, restore=False)
+    assert plan.n_exchanges == 2
+    assert sorted(plan.final_where) == list(range(n)) and plan.final_where != list(range(n))
+    p = np.arange(1 << n)
+    k = np.zeros_like(p)
+    for b in range(n):
+        k |= ((p >> plan.final_where[b]) & 1) << b
+    assert np.abs(got - orc.qft_reference(x)[k]).max() < 1e-12
+    full, plan3 = run_emulated(prog.records(), prog.pool(), n, world, x, restore=True)
+    assert plan3.n_exchanges == 3 and np.abs(full - orc.qft_reference(x)).max() < 1e-12
 
 
 @pytest.mark.parametrize("world", [2, 4])
