@@ -1,6 +1,5 @@
-"""Window optimiser over compiled gate trees, with its equivalence check run on the GPU."""
-from .basic_optimizer import SlidingWindowCombiner, prune
+"""Peephole optimiser over flattened gate records, with its equivalence check run on the GPU."""
+from .peephole import RecordPeephole, grain_of, optimize_leaves, peephole_records
 from .verify import equal_on_device, optimize_checked
-from .window import AnnihilateOperator, ConsolidateOperator
 
-__all__ = ["SlidingWindowCombiner", "prune", "AnnihilateOperator", "ConsolidateOperator", "equal_on_device", "optimize_checked"]
+__all__ = ["RecordPeephole", "optimize_leaves", "peephole_records", "grain_of", "equal_on_device", "optimize_checked"]

@@ -1,15 +1,14 @@
-"""Window optimiser (quantum_simulations_b200/optimize) against the reference's own results: golden
-fixtures written by ``oracle/gen_golden.py optimizer`` hold, for compiled streams and hand-made sequences, the leaves
-before and after the REAL ``SlidingWindowCombiner``; the mirror must produce the same leaves.  The operator must not
-change (oracle on CPU; ``verify.equal_on_device`` on the GPU)."""
+"""Peephole pass over gate records (quantum_simulations_b200/optimize/peephole.py) against the reference's
+own results: golden fixtures written by ``oracle/gen_golden.py optimizer`` hold, for compiled streams and hand-made
+sequences, the leaves before and after the REAL ``SlidingWindowCombiner``; the record-level pass must leave the same
+gates.  The operator must not change (oracle on CPU; ``verify.equal_on_device`` on the GPU)."""
 import numpy as np
 import pytest
 
 import quantum_simulations_b200 as qs
 from oracle import sv_oracle as orc
 from quantum_simulations_b200.construct.bytecode import Bytecode, BytecodeIter
-from quantum_simulations_b200.optimize import SlidingWindowCombiner
-from quantum_simulations_b200.utils.granularity import granularity
+from quantum_simulations_b200.optimize import RecordPeephole, grain_of, optimize_leaves, peephole_records
 from tests.golden_io import load, unpack_gates
 
 D = load("optimizer")
@@ -18,9 +17,7 @@ T, C1 = qs.QType.TARGET, qs.QType.CONTROL1
 
 
 def _run(leaves, window, emit):
-    root = Bytecode(np.eye(2), [Bytecode(g) for g in leaves])
-    out = SlidingWindowCombiner(window=window, emit=qs.GateGrain[emit]).optimize(root)
-    return [a.data for a in BytecodeIter(out) if a.is_leaf() and not a.skip and hasattr(a.data, "controls")]
+    return optimize_leaves(leaves, window, qs.GateGrain[emit])
 
 
 @pytest.mark.parametrize("name", CASES)
@@ -71,7 +68,25 @@ def test_textbook_rewrites():
     # window = 1 lets a leaf see one predecessor only: T T T T -> S S (pairs), not Z
     assert [g.gate for g in _run([g1(U.T, 0)] * 4, 1, "CLIFFORD_T")] == [U.S, U.S]
     assert [g.gate for g in _run([g1(U.T, 0)] * 4, 0, "CLIFFORD_T")] == [U.Z]
-    assert granularity(cx) == qs.GateGrain.CLIFFORD_T and granularity(qs.UnitaryM(4, (0, 3), np.eye(2))) == qs.GateGrain.TWO_LEVEL
+    assert grain_of(np.array(U.X), 1) == qs.GateGrain.CLIFFORD_T and grain_of(np.array(U.X), 2) == qs.GateGrain.SINGLET
+    assert grain_of(np.array(U.Y), 0) == qs.GateGrain.CTRL_PRUNED and grain_of(np.eye(4), 0) == qs.GateGrain.MULTI_TARGET
+
+
+def test_record_level_interface():
+    """The pass proper sees nothing but qsv_gate_t records and the matrix pool."""
+    from quantum_simulations_b200.program import flatten
+    q = [qs.Qubit(i) for i in range(3)]
+    U = qs.UnivGate
+    g1 = lambda g, t: qs.CtrlGate(g, [T], [q[t]])  # noqa: E731
+    cx = qs.CtrlGate(U.X, [C1, T], [q[0], q[1]])
+    prog = flatten([g1(U.T, 2), cx, g1(U.T, 2), cx, g1(U.H, 0), g1(U.H, 0), g1(U.S, 1)])
+    keep, mats, absorbed = peephole_records(prog.records(0), prog.pool())
+    assert keep == [2, 6] and absorbed[2] == [0] and absorbed[6] == []
+    assert np.allclose(mats[2], np.array(U.S)) and np.allclose(mats[6], np.array(U.S))
+    # the tree-level wrapper keeps non-gate leaves as fences
+    root = Bytecode(np.eye(2), [Bytecode(g1(U.X, 0)), Bytecode(qs.UnitaryM(8, (0, 3), np.array(U.X))), Bytecode(g1(U.X, 0))])
+    out = RecordPeephole().optimize(root)
+    assert len([a for a in BytecodeIter(out) if a.is_leaf()]) == 3
 
 
 @pytest.mark.gpu
@@ -80,7 +95,7 @@ def test_optimiser_checked_on_the_gpu():
     for name in ("r4ct", "r4pr", "hand_w0", "r8sg"):
         before = unpack_gates(D, name + "_before")
         root = Bytecode(np.eye(2), [Bytecode(g) for g in before])
-        opt = SlidingWindowCombiner(window=int(D[name + "_window"]), emit=qs.GateGrain[str(D[name + "_emit"])])
+        opt = RecordPeephole(window=int(D[name + "_window"]), emit=qs.GateGrain[str(D[name + "_emit"])])
         out = optimize_checked(root, opt)
         after = [a.data for a in BytecodeIter(out) if a.is_leaf() and not a.skip]
         assert len(after) == len(unpack_gates(D, name + "_after"))
@@ -102,7 +117,7 @@ def test_verify_plumbing_with_a_host_engine(monkeypatch):
     for name in ("r4ct", "r4pr", "hand_w0", "r8sg"):
         before = unpack_gates(D, name + "_before")
         root = Bytecode(np.eye(2), [Bytecode(g) for g in before])
-        opt = SlidingWindowCombiner(window=int(D[name + "_window"]), emit=qs.GateGrain[str(D[name + "_emit"])])
+        opt = RecordPeephole(window=int(D[name + "_window"]), emit=qs.GateGrain[str(D[name + "_emit"])])
         out = optimize_checked(root, opt)
         after = [a.data for a in BytecodeIter(out) if a.is_leaf() and not a.skip]
         assert len(after) == len(unpack_gates(D, name + "_after"))
