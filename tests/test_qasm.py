@@ -185,3 +185,96 @@ def test_unitary_plumbing_with_a_host_engine(monkeypatch):
     full = b.finish().unitary()
     assert full.shape == (4, 4) and abs(full[0b11, 0] - 1 / np.sqrt(2)) < 1e-12
     assert b.finish().unitary(drop_ancilla=True).shape == (2, 2)
+
+
+# ---- hand-written known-answer files (tests/golden/qasm/README.md) -------------------------------------------------
+def _kron(*ms):
+    out = np.eye(1)
+    for m in ms:
+        out = np.kron(out, m)
+    return out
+
+
+def _ctrl(n, controls, target, m):
+    """Operator over n qubits (qubit 0 most significant): `m` on `target` where every (qubit, value) in `controls` holds."""
+    dim = 1 << n
+    out = np.zeros((dim, dim), dtype=complex)
+    for col in range(dim):
+        bit = lambda q, x=col: (x >> (n - 1 - q)) & 1  # noqa: E731
+        if all(bit(q) == v for q, v in controls):
+            for r in (0, 1):
+                row = (col & ~(1 << (n - 1 - target))) | (r << (n - 1 - target))
+                out[row, col] += m[r, bit(target)]
+        else:
+            out[col, col] = 1
+    return out
+
+
+def _known_answers():
+    I2 = np.eye(2)
+    X = np.array([[0, 1], [1, 0]], dtype=complex)
+    Y = np.array([[0, -1j], [1j, 0]])
+    Z = np.diag([1, -1]).astype(complex)
+    H = np.array([[1, 1], [1, -1]]) / np.sqrt(2)
+    rx = lambda t: np.array([[np.cos(t / 2), -1j * np.sin(t / 2)], [-1j * np.sin(t / 2), np.cos(t / 2)]])  # noqa: E731
+    ry = lambda t: np.array([[np.cos(t / 2), -np.sin(t / 2)], [np.sin(t / 2), np.cos(t / 2)]], dtype=complex)  # noqa: E731
+    rz = lambda t: np.diag([np.exp(-0.5j * t), np.exp(0.5j * t)])  # noqa: E731
+    ph = lambda t: np.diag([1, np.exp(1j * t)])  # noqa: E731
+    t_, p_, l_ = 1.2, -0.4, 2.2
+    u = np.array([[np.cos(t_ / 2), -np.exp(1j * l_) * np.sin(t_ / 2)],
+                  [np.exp(1j * p_) * np.sin(t_ / 2), np.exp(1j * (p_ + l_)) * np.cos(t_ / 2)]])   # OpenQASM 3.0 spec, built-in U
+    return {
+        "bell": _ctrl(2, [(0, 1)], 1, X) @ _kron(H, I2),
+        "mixed_controls": _ctrl(3, [(0, 1), (1, 0)], 2, X),
+        "controlled_phase": _kron(np.diag([np.exp(0.5j * np.pi), 1]), I2) @ _kron(I2, ph(np.pi / 4)),
+        "u_and_gphase": np.exp(0.25j) * u,
+        "rotations": _kron(np.diag([1, np.exp(-0.25j * np.pi)]), I2) @ _kron(I2, np.diag([1, -1j])) @ _ctrl(2, [(1, 0)], 0, rz(0.5))
+                     @ _kron(rz(2.0), I2) @ _kron(I2, ry(-1.1)) @ _kron(rx(0.3), I2),
+        "ancilla_register": _kron(Y, I2, I2) @ _ctrl(3, [(0, 1), (1, 1)], 2, Z) @ _ctrl(3, [(2, 1)], 1, H),
+    }
+
+
+def _golden_text(name):
+    import os
+    return open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "qasm", name + ".qasm")).read()
+
+
+@pytest.mark.parametrize("name", ["bell", "mixed_controls", "controlled_phase", "u_and_gphase", "rotations", "ancilla_register"])
+def test_reader_on_hand_written_known_answers(name):
+    """The reader is pinned to files it did not write: each hand-written OpenQASM 3 program must parse into the
+    operator worked out independently from the specification (ancillas counted as ordinary qubits)."""
+    prog = parse_qasm(_golden_text(name), ancilla_as_plain=True)
+    assert np.abs(_unitary_of(prog) - _known_answers()[name]).max() < 1e-13
+
+
+def test_writer_emits_the_hand_written_statements():
+    """... and the writer to the same files: gate objects -> exactly the statements of the hand-written text."""
+    q = [qs.Qubit(i) for i in range(3)]
+    a0 = qs.Qubit(7, ancilla=True)
+    U = qs.UnivGate
+
+    def body(text):
+        return [ln.strip() for ln in text.splitlines() if ln.strip() and not ln.startswith(("OPENQASM", "include", "qubit", "//"))]
+
+    def emit(gates, extra=()):
+        b = QasmBuilder()
+        b.register(list(extra))
+        for g in gates:
+            b.register(g.qspace)
+            b.build_gate(g)
+        return body(b.finish().qasm())
+
+    assert emit([qs.CtrlGate(U.H, [T], [q[0]]), qs.CtrlGate(U.X, [C1, T], [q[0], q[1]])]) == body(_golden_text("bell"))
+    assert emit([qs.CtrlGate(U.X, [C1, C0, T], q)]) == body(_golden_text("mixed_controls"))
+    rot = [qs.CtrlGate(qs.RGate(0.3, qs.PrincipalAxis.X), [T], [q[0]]), qs.CtrlGate(qs.RGate(-1.1, qs.PrincipalAxis.Y), [T], [q[1]]),
+           qs.CtrlGate(qs.RGate(2.0, qs.PrincipalAxis.Z), [T], [q[0]]), qs.CtrlGate(qs.RGate(0.5, qs.PrincipalAxis.Z), [C0, T], [q[1], q[0]]),
+           qs.CtrlGate(U.SD, [T], [q[1]]), qs.CtrlGate(U.TD, [T], [q[0]])]
+    assert emit(rot) == body(_golden_text("rotations"))
+    anc = [qs.CtrlGate(U.H, [C1, T], [a0, q[1]]), qs.CtrlGate(U.Z, [C1, C1, T], [q[0], q[1], a0]), qs.CtrlGate(U.Y, [T], [q[0]])]
+    assert emit(anc) == body(_golden_text("ancilla_register"))
+    # a general one-qubit unitary goes out as gphase + U with the angles of the specification's U
+    t_, p_, l_ = 1.2, -0.4, 2.2
+    lines = emit([qs.CtrlGate(np.exp(0.25j) * u_matrix(t_, p_, l_), [T], [q[0]])])
+    assert len(lines) == 2 and lines[0].startswith("gphase(") and lines[1].startswith("U(") and lines[1].endswith(" q[0];")
+    got = [float(x) for x in lines[1][2:lines[1].index(")")].split(",")] + [float(lines[0][7:lines[0].index(")")])]
+    assert np.allclose(got, [t_, p_, l_, 0.25], atol=1e-12)
