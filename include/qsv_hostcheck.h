@@ -1,4 +1,5 @@
-/* qsv_hostcheck.h -- TEST INFRASTRUCTURE exported by libqsv.so next to the product ABI (qsv.h).
+/* qsv_hostcheck.h -- TEST INFRASTRUCTURE exported by libqsv_hostcheck.so, a library of its own built from the product's
+ * objects plus csrc/qsv_hostcheck.cu; the product library libqsv.so does not contain it.
  *
  * One entry point that interprets the FUSED PLAN of a gate program on the host, so that the fusion pass
  * (host code: stage selection, phase polynomials, SWAP relabelling, launch budgets, FFT-shape conversion,

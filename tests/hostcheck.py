@@ -11,16 +11,17 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from quantum_simulations_b200 import _lib  # noqa: E402
 
+HOSTCHECK_PATH = os.path.join(os.path.dirname(_lib.LIB_PATH), "libqsv_hostcheck.so")   # built next to libqsv.so, never loaded by the package
 _fn = None
 
 
 def _load():
     global _fn
     if _fn is None:
-        if not os.path.exists(_lib.LIB_PATH):
+        if not os.path.exists(HOSTCHECK_PATH):
             import __graft_entry__
             __graft_entry__.build()
-        lib = C.CDLL(_lib.LIB_PATH)
+        lib = C.CDLL(HOSTCHECK_PATH)
         _fn = lib.qsv_hostcheck_fused
         _fn.restype = C.c_int
         _fn.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p,

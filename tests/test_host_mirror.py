@@ -186,7 +186,9 @@ def test_library_exports_every_declared_symbol():
     hc = open(os.path.join(ROOT, "include", "qsv_hostcheck.h")).read()
     hc_declared = set(re.findall(r"\b(qsv_[a-z0-9_]+)\s*\(", hc))
     assert hc_declared == {"qsv_hostcheck_fused"}
-    assert hasattr(lib, "qsv_hostcheck_fused")
+    assert not hasattr(lib, "qsv_hostcheck_fused"), "the host interpreter must not be part of the product library"
+    from tests.hostcheck import HOSTCHECK_PATH
+    assert hasattr(ctypes.CDLL(HOSTCHECK_PATH), "qsv_hostcheck_fused")
     assert "qsv_hostcheck_fused" not in _lib.exported_symbols()
     assert b"sm_100a" in ctypes.cast(lib.qsv_version, ctypes.CFUNCTYPE(ctypes.c_char_p))()
 
