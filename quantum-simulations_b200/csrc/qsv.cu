@@ -81,6 +81,34 @@ __global__ void __launch_bounds__(256) k_gate1(typename cplx_of<R>::type* __rest
     }
 }
 
+// K1 for a LOW target bit (below the warp width), uncontrolled: every lane loads ONE amplitude (a warp reads 512 contiguous
+// bytes), gets its partner from lane ^ 2^t with warp shuffles, and writes its own output -- the "warp-shuffle exchange for
+// low-index target qubits".  k_gate1 handles the same gates by giving each thread both amplitudes of a pair (32 contiguous
+// bytes per thread for t = 0); which one is faster is an A/B kept in profiles/ (QSV_SHFL=1 selects this kernel).
+template <typename R, int U>
+__global__ void __launch_bounds__(256) k_gate1_shfl(typename cplx_of<R>::type* __restrict__ st, uint64_t namps, int t, Mat2 mat) {
+    typedef typename cplx_of<R>::type C;
+    const uint64_t base = (uint64_t)blockIdx.x * (256 * U) + threadIdx.x;
+    const bool hi = (threadIdx.x >> t) & 1;   // (the index bits below 8 are the thread's own: stride 256 between its amplitudes)
+    // row of the matrix this lane computes: out = m_self * own + m_other * partner
+    const C m_self = hi ? cmake<C, R>((R)mat.m[6], (R)mat.m[7]) : cmake<C, R>((R)mat.m[0], (R)mat.m[1]);
+    const C m_other = hi ? cmake<C, R>((R)mat.m[4], (R)mat.m[5]) : cmake<C, R>((R)mat.m[2], (R)mat.m[3]);
+    C a[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const uint64_t p = base + (uint64_t)u * 256;
+        a[u] = p < namps ? st[p] : cmake<C, R>((R)0, (R)0);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        C b;
+        b.x = __shfl_xor_sync(0xffffffffu, a[u].x, 1 << t);
+        b.y = __shfl_xor_sync(0xffffffffu, a[u].y, 1 << t);
+        const uint64_t p = base + (uint64_t)u * 256;
+        if (p < namps) st[p] = cfma(m_other, b, cmul(m_self, a[u]));
+    }
+}
+
 // K3 special case diag(1, d): only amplitudes with the target bit set are touched
 template <typename R, int U>
 __global__ void __launch_bounds__(256) k_phase1(typename cplx_of<R>::type* __restrict__ st, uint64_t namps,
@@ -444,6 +472,15 @@ static int launch_gate1(qsv_ctx* ctx, void* state, int n_bits, const qsv_gate_t*
         k_phase1<R, U><<<(unsigned)blocks, 256, 0, s>>>((C*)state, namps, ins, mat[6], mat[7]);
         ctx->stats.amp_bytes += 2 * namps * sizeof(C);
     } else {
+        static const bool use_shfl = getenv("QSV_SHFL") != nullptr;  // measured no faster than the pair kernel (profiles/r2_ab_shuffle.txt)
+        if (use_shfl && kind == QSV_DENSE1 && g->ctrl_mask == 0 && g->target_bits[0] < 5 && n_bits >= 5) {
+            const uint64_t namps = 1ull << n_bits;
+            const uint64_t blocks = (namps + 256 * U - 1) / (256 * U);
+            k_gate1_shfl<R, U><<<(unsigned)blocks, 256, 0, s>>>((C*)state, namps, (int)g->target_bits[0], m2);
+            ctx->stats.amp_bytes += 2 * namps * sizeof(C);
+            ctx->stats.kernel_launches++;
+            return QSV_OK;
+        }
         if ((rc = build_insert(ctx, g, n_bits, &ins, true))) return rc;
         const uint64_t npairs = 1ull << (n_bits - ins.n);
         const uint64_t blocks = (npairs + 256 * U - 1) / (256 * U);

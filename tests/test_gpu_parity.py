@@ -518,3 +518,37 @@ def test_dela_with_a_state_other_than_ket0(fuse):
             continue
         got = g.sorted().dela(d["state"][i]).inflate()
         assert np.abs(got - r.sorted().inflate()).max() < TOL128, i
+
+
+def test_warp_shuffle_kernel_for_low_target_bits():
+    """QSV_SHFL=1 routes uncontrolled dense gates on index bits 0..4 through k_gate1_shfl (partner amplitude fetched with
+    warp shuffles).  The switch is read once per process, so the run happens in a child process; result against the oracle."""
+    import os
+    import subprocess
+    import sys
+    code = r"""
+import numpy as np, sys
+sys.path.insert(0, %r)
+import quantum_simulations_b200 as qs
+from quantum_simulations_b200.engine import apply_circuit
+from quantum_simulations_b200.program import Program
+from oracle import sv_oracle as orc
+rng = np.random.default_rng(5)
+n = 12
+prog = Program([qs.Qubit(i) for i in range(n)])
+for _ in range(40):
+    a = rng.standard_normal((2, 2)) + 1j * rng.standard_normal((2, 2))
+    q, r = np.linalg.qr(a)
+    prog.add_raw([int(rng.integers(0, 7))], 0, 0, q)
+for dt, tol in ((np.complex128, 1e-10), (np.complex64, 1e-5)):
+    x = rng.standard_normal((1 << n, 2)) + 1j * rng.standard_normal((1 << n, 2))
+    got = apply_circuit(prog, x, fuse=False, dtype=dt)
+    ref = x.astype(np.complex128).reshape(-1).copy()
+    orc.run_records(prog.records(1), prog.pool(), ref, n + 1)
+    err = np.abs(got - ref.reshape(1 << n, 2)).max()
+    assert err < tol * np.abs(ref).max(), err
+print("ok")
+""" % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, QSV_SHFL="1")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
