@@ -206,6 +206,12 @@ int qsv_allprop(qsv_ctx* ctx, const void* a, const void* b, uint64_t n_amps, dou
  *  - Makes `device` current.  The first call on each device looks up the array's device address
  *    (a one-off cudaGetSymbolAddress); make that first call before starting any stream capture.
  *    Not thread-safe against another first call on the same device.
+ *  - That first call is also where the CUDA runtime may create the device's context and load this
+ *    library's code image (kernels and the 16 KiB array) onto the device -- work the RUNTIME does with
+ *    device memory of its own.  On a device that is already full it can therefore fail with an
+ *    out-of-memory error even though this function allocates nothing: make one warm-up call per
+ *    device at start-up, before handing the memory out (n_amps = 0 is enough; it performs the whole
+ *    set-up and returns max = 0, bad = 0).  Later calls do no set-up.
  *  - All calls on a device share the one array.  Each call overwrites every slot it later
  *    reads, so contents left by the previous call are harmless; but two calls whose kernels
  *    overlap on the GPU (different streams, or different host threads) race on it and give

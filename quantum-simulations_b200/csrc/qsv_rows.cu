@@ -10,11 +10,14 @@
 // and the kernel keeps a slab of C columns x all rows resident in shared memory while it walks the
 // whole op list: HBM traffic is one read and one write of the state for the entire program.
 //
-// Columns are independent, so lane t of the (single) warp of a CTA owns column t of the slab and never
-// synchronises with other lanes; ops are staged into shared memory in double-buffered cp.async chunks.
-// The row shared by consecutive ops (Givens rotations of one column of the QR sweep all touch the pivot
-// row) stays in registers.  Throughput is bound by the dependent chain through that pivot row, not by
-// HBM: the 16 MiB state of config 4 is read and written once.
+// Scheduling (round 2).  The first version gave every column to one lane of a single warp and walked the op list in order:
+// 8 busy lanes per CTA and a dependent chain of half a million ops through shared memory (55.7 ms for config 4, 106 ns per
+// op).  The chain is a property of that schedule, not of the problem: two row-pair ops depend on each other only if they
+// share a row.  The host therefore LEVELS the ops -- level(op) = 1 + max(level of the last op on either of its rows) -- and
+// sorts them by level (stable).  All ops of a level touch pairwise disjoint rows, so a CTA of up to 1024 threads applies
+// them at once, one (op, column) pair per thread, with ONE CTA barrier per level; for the Givens QR stream of a 1024 x 1024
+// unitary that is ~3 000 levels of ~175 ops instead of 523 776 sequential ops.  The ops of the next level are fetched into
+// registers before the barrier, so their L2 latency hides behind the current level's arithmetic.
 #include <algorithm>
 
 #include "qsv_common.cuh"
@@ -27,90 +30,83 @@ struct __align__(16) RowOp {  // 80 bytes
 };
 static_assert(sizeof(RowOp) == 80, "RowOp layout");
 
-#define ROW_CHUNK 64  // ops per staged chunk (5 KB)
-
 struct RowSlabPlan {
-    RowOp* d_ops = nullptr;
-    uint64_t n_ops = 0;
+    RowOp* d_ops = nullptr;          // sorted by level
+    uint32_t* d_level_start = nullptr;  // [n_levels + 1] offsets into d_ops
+    uint64_t n_ops = 0, n_levels = 0;
     uint64_t n_source_gates = 0;
     uint64_t dim = 0, batch = 0;
-    int cols = 0;  // columns per CTA
+    int cols = 0;     // columns per CTA (power of two)
+    int threads = 0;  // CTA size
     ~RowSlabPlan() {
         if (d_ops) cudaFree(d_ops);
+        if (d_level_start) cudaFree(d_level_start);
     }
 };
 
 template <typename R>
-__global__ void __launch_bounds__(32, 1) k_rowslab(typename cplx_of<R>::type* __restrict__ st, uint64_t dim, uint64_t batch,
-                                                   int cols, const RowOp* __restrict__ ops, uint64_t n_ops) {
+__global__ void __launch_bounds__(1024, 1) k_rowlevels(typename cplx_of<R>::type* __restrict__ st, uint64_t dim, uint64_t batch, int cols_log2,
+                                                      const RowOp* __restrict__ ops, const uint32_t* __restrict__ level_start,
+                                                      uint32_t n_levels) {
     typedef typename cplx_of<R>::type C;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    RowOp* opbuf = reinterpret_cast<RowOp*>(smem_raw);                        // 2 x ROW_CHUNK ops
-    C* slab = reinterpret_cast<C*>(smem_raw + 2 * ROW_CHUNK * sizeof(RowOp));  // [dim][cols]
-    const int lane = threadIdx.x;
-    const uint64_t col0 = (uint64_t)blockIdx.x * cols;
-    // load the slab (each row segment is cols x 16 B contiguous)
-    for (uint64_t i = lane; i < dim * cols; i += 32) {
-        const uint64_t r = i / cols, c = i % cols;
-        slab[i] = st[r * batch + col0 + c];
-    }
-    auto stage = [&](uint64_t chunk, int buf) {
-        const uint64_t first = chunk * ROW_CHUNK;
-        const uint64_t n = min((uint64_t)ROW_CHUNK, n_ops - first);
-        const char* src = reinterpret_cast<const char*>(ops + first);
-        char* dst = reinterpret_cast<char*>(opbuf + buf * ROW_CHUNK);
-        for (uint64_t b = (uint64_t)lane * 16; b < n * sizeof(RowOp); b += 32 * 16) {
-            const uint32_t s = (uint32_t)__cvta_generic_to_shared(dst + b);
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(src + b));
+    C* slab = reinterpret_cast<C*>(smem_raw);  // [dim][cols]
+    const uint32_t tid = threadIdx.x, T = blockDim.x;
+    const uint32_t cols = 1u << cols_log2, cmask = cols - 1u;
+    const uint64_t col0 = (uint64_t)blockIdx.x << cols_log2;
+    const uint64_t slab_amps = dim << cols_log2;
+    for (uint64_t i = tid; i < slab_amps; i += T) slab[i] = st[(i >> cols_log2) * batch + col0 + (i & cmask)];
+    // one (op, column) item per thread and level in the common case; the first item of the NEXT level is fetched early
+    uint32_t s = n_levels ? level_start[0] : 0, e = n_levels ? level_start[1] : 0;
+    uint32_t s2 = e, e2 = n_levels > 1 ? level_start[2] : e;
+    RowOp op;
+    bool have = false;
+    auto fetch = [&](uint32_t first, uint32_t last, RowOp& o) {
+        const uint32_t idx = first + (tid >> cols_log2);
+        if (idx < last) {
+            const uint4* p = reinterpret_cast<const uint4*>(ops + idx);
+            uint4* q = reinterpret_cast<uint4*>(&o);
+#pragma unroll
+            for (int w = 0; w < 5; ++w) q[w] = __ldg(p + w);
+            return true;
         }
-        asm volatile("cp.async.commit_group;\n" ::);
+        return false;
     };
-    const uint64_t n_chunks = (n_ops + ROW_CHUNK - 1) / ROW_CHUNK;
-    if (n_chunks) stage(0, 0);
-    __syncwarp();
-    const bool active = lane < cols;
-    uint32_t cached = 0xFFFFFFFFu;  // row whose value for this lane's column is held in `cv`
-    C cv = cmake<C, R>((R)0, (R)0);
-    for (uint64_t ch = 0; ch < n_chunks; ++ch) {
-        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-        __syncwarp();
-        if (ch + 1 < n_chunks) stage(ch + 1, (int)((ch + 1) & 1));
-        const RowOp* cur = opbuf + (ch & 1) * ROW_CHUNK;
-        const int n = (int)min((uint64_t)ROW_CHUNK, n_ops - ch * ROW_CHUNK);
-        if (active) {
-            for (int i = 0; i < n; ++i) {
-                const RowOp& op = cur[i];
-                const uint32_t r0 = op.r0, r1 = op.r1;
-                if (cached != r0) {
-                    if (cached != 0xFFFFFFFFu) slab[(uint64_t)cached * cols + lane] = cv;
-                    cv = slab[(uint64_t)r0 * cols + lane];
-                    cached = r0;
-                }
-                // (r1 == cached cannot happen: r1 != r0 and cached == r0 here)
-                const C a1 = slab[(uint64_t)r1 * cols + lane];
-                C b1;
-                if (op.swap) {
-                    b1 = cv;
-                    cv = a1;
-                } else {
-                    const C m00 = cmake<C, R>((R)op.m[0], (R)op.m[1]), m01 = cmake<C, R>((R)op.m[2], (R)op.m[3]);
-                    const C m10 = cmake<C, R>((R)op.m[4], (R)op.m[5]), m11 = cmake<C, R>((R)op.m[6], (R)op.m[7]);
-                    const C a0 = cv;
-                    cv = cfma(m01, a1, cmul(m00, a0));
-                    b1 = cfma(m11, a1, cmul(m10, a0));
-                }
-                slab[(uint64_t)r1 * cols + lane] = b1;
-            }
+    auto apply = [&](const RowOp& o, uint32_t col) {
+        C* p0 = slab + ((uint64_t)o.r0 << cols_log2) + col;
+        C* p1 = slab + ((uint64_t)o.r1 << cols_log2) + col;
+        const C a0 = *p0, a1 = *p1;
+        if (o.swap) {
+            *p0 = a1;
+            *p1 = a0;
+        } else {
+            const C m00 = cmake<C, R>((R)o.m[0], (R)o.m[1]), m01 = cmake<C, R>((R)o.m[2], (R)o.m[3]);
+            const C m10 = cmake<C, R>((R)o.m[4], (R)o.m[5]), m11 = cmake<C, R>((R)o.m[6], (R)o.m[7]);
+            *p0 = cfma(m01, a1, cmul(m00, a0));
+            *p1 = cfma(m11, a1, cmul(m10, a0));
         }
-        __syncwarp();
+    };
+    have = fetch(s, e, op);
+    __syncthreads();
+    const uint32_t per_pass = T >> cols_log2;  // ops one pass of the CTA covers
+    for (uint32_t l = 0; l < n_levels; ++l) {
+        RowOp nxt;
+        const bool have_next = (l + 1 < n_levels) && fetch(s2, e2, nxt);
+        const uint32_t e3 = (l + 2 < n_levels) ? level_start[l + 3] : e2;
+        if (have) apply(op, tid & cmask);
+        for (uint32_t first = s + per_pass; first < e; first += per_pass) {  // (levels wider than the CTA: rare)
+            RowOp more;
+            if (fetch(first, e, more)) apply(more, tid & cmask);
+        }
+        __syncthreads();
+        s = s2;
+        e = e2;
+        s2 = e2;
+        e2 = e3;
+        op = nxt;
+        have = have_next;
     }
-    if (active && cached != 0xFFFFFFFFu) slab[(uint64_t)cached * cols + lane] = cv;
-    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-    __syncwarp();
-    for (uint64_t i = lane; i < dim * cols; i += 32) {
-        const uint64_t r = i / cols, c = i % cols;
-        st[r * batch + col0 + c] = slab[i];
-    }
+    for (uint64_t i = tid; i < slab_amps; i += T) st[(i >> cols_log2) * batch + col0 + (i & cmask)] = slab[i];
 }
 
 void rowslab_free(RowSlabPlan* p) { delete p; }
@@ -126,7 +122,7 @@ int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out) {
     const uint64_t qmask = (dim - 1) << b;
     // columns per CTA: as many as fit next to the op buffers in ~200 KB, at most a warp and at most the batch
     const size_t amp = amp_size(ctx->dtype);
-    const size_t budget = 200 * 1024 - 2 * ROW_CHUNK * sizeof(RowOp);
+    const size_t budget = 200 * 1024;
     uint64_t cols = budget / (dim * amp);
     if (cols < 1) return QSV_E_UNSUPPORTED;
     cols = std::min<uint64_t>(std::min<uint64_t>(cols, 32), batch);
@@ -184,23 +180,50 @@ int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out) {
             inv[i] = (uint32_t)i;
         }
     }
+    // level schedule: an op waits only for the last op on either of its rows
+    std::vector<uint32_t> level(ops.size()), last(dim, 0);
+    uint32_t n_levels = 0;
+    for (size_t i = 0; i < ops.size(); ++i) {
+        const uint32_t lv = std::max(last[ops[i].r0], last[ops[i].r1]) + 1;
+        level[i] = lv - 1;
+        last[ops[i].r0] = last[ops[i].r1] = lv;
+        n_levels = std::max(n_levels, lv);
+    }
+    std::vector<uint32_t> start(n_levels + 3, 0);  // (+2 padding entries: the kernel reads two levels ahead)
+    for (size_t i = 0; i < ops.size(); ++i) start[level[i] + 1]++;
+    for (uint32_t l = 0; l < n_levels; ++l) start[l + 1] += start[l];
+    start[n_levels + 1] = start[n_levels + 2] = start[n_levels];
+    std::vector<RowOp> sorted(ops.size());
+    {
+        std::vector<uint32_t> fill(start.begin(), start.begin() + n_levels + 1);
+        for (size_t i = 0; i < ops.size(); ++i) sorted[fill[level[i]]++] = ops[i];
+    }
     RowSlabPlan* plan = new RowSlabPlan();
     plan->n_ops = ops.size();
+    plan->n_levels = n_levels;
     plan->n_source_gates = ctx->gates.size();
     plan->dim = dim;
     plan->batch = batch;
     plan->cols = (int)cols;
+    {
+        // CTA size: enough threads for the widest common level (dim/2 ops at most), a multiple of the warp, at most 1024
+        uint64_t want = std::min<uint64_t>((dim / 2) * cols, 1024);
+        want = std::max<uint64_t>(want, std::max<uint64_t>(32, cols));
+        plan->threads = (int)((want + 31) / 32 * 32);
+    }
     if (!ops.empty()) {
-        cudaError_t e = cudaMalloc(&plan->d_ops, ops.size() * sizeof(RowOp));
-        if (e == cudaSuccess) e = cudaMemcpy(plan->d_ops, ops.data(), ops.size() * sizeof(RowOp), cudaMemcpyHostToDevice);
+        cudaError_t e = cudaMalloc(&plan->d_ops, sorted.size() * sizeof(RowOp));
+        if (e == cudaSuccess) e = cudaMemcpy(plan->d_ops, sorted.data(), sorted.size() * sizeof(RowOp), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMalloc(&plan->d_level_start, start.size() * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaMemcpy(plan->d_level_start, start.data(), start.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
         if (e != cudaSuccess) {
             delete plan;
             return qsv_fail(ctx, QSV_E_CUDA, "uploading the row-op stream failed: %s", cudaGetErrorString(e));
         }
     }
-    const int smem = (int)(2 * ROW_CHUNK * sizeof(RowOp) + dim * cols * amp);
-    cudaError_t e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_rowslab<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                                           : cudaFuncSetAttribute(k_rowslab<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const int smem = (int)(dim * cols * amp);
+    cudaError_t e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_rowlevels<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                                           : cudaFuncSetAttribute(k_rowlevels<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
         delete plan;
         return qsv_fail(ctx, QSV_E_CUDA, "cudaFuncSetAttribute(%d B smem) failed: %s", smem, cudaGetErrorString(e));
@@ -211,14 +234,20 @@ int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out) {
 
 int rowslab_run(qsv_ctx* ctx, RowSlabPlan* plan, void* state, cudaStream_t stream) {
     const size_t amp = amp_size(ctx->dtype);
-    const size_t smem = 2 * ROW_CHUNK * sizeof(RowOp) + plan->dim * plan->cols * amp;
+    const size_t smem = plan->dim * plan->cols * amp;
     const unsigned grid = (unsigned)(plan->batch / plan->cols);
-    if (ctx->dtype == QSV_C128)
-        k_rowslab<double><<<grid, 32, smem, stream>>>((double2*)state, plan->dim, plan->batch, plan->cols, plan->d_ops, plan->n_ops);
-    else
-        k_rowslab<float><<<grid, 32, smem, stream>>>((float2*)state, plan->dim, plan->batch, plan->cols, plan->d_ops, plan->n_ops);
-    QSV_CUDA(ctx, cudaGetLastError());
-    ctx->stats.kernel_launches++;
+    int cl = 0;
+    while ((1 << cl) < plan->cols) ++cl;
+    if (plan->n_ops) {
+        if (ctx->dtype == QSV_C128)
+            k_rowlevels<double><<<grid, plan->threads, smem, stream>>>((double2*)state, plan->dim, plan->batch, cl, plan->d_ops,
+                                                                      plan->d_level_start, (uint32_t)plan->n_levels);
+        else
+            k_rowlevels<float><<<grid, plan->threads, smem, stream>>>((float2*)state, plan->dim, plan->batch, cl, plan->d_ops,
+                                                                     plan->d_level_start, (uint32_t)plan->n_levels);
+        QSV_CUDA(ctx, cudaGetLastError());
+        ctx->stats.kernel_launches++;
+    }
     ctx->stats.sweeps++;
     ctx->stats.fused_sweeps++;
     ctx->stats.amp_bytes += 2 * amp * plan->dim * plan->batch;

@@ -171,8 +171,11 @@ def test_swaps_are_relabelled_and_layout_is_restored(n, batch):
 
 
 def test_builder_conformance_template():
-    """The five checks of the reference's CircuitTestTemplate (circuit_test_template.py:21-113), with
-    the expected matrices taken from the oracle's restatement of inflate()."""
+    """The five checks of the reference's CircuitTestTemplate (circuit_test_template.py:21-113), restated rather than
+    imported (the template lives in the reference's test tree, absent on the GPU box), with the expected matrices taken
+    from the oracle's restatement of inflate() -- itself pinned to the reference's inflate() goldens.  The ten random
+    gates are drawn from this test's own seeds, NOT the reference's parametrised ones (circuit_test_template.py:52-55):
+    the reference's seeds feed its own mgen/scipy streams, which need the reference to reproduce."""
     def run(gates, expected, register=None):
         b = qs.get_builder(qs.QompilePlatform.B200)
         for cu in gates:
