@@ -134,6 +134,23 @@ int qsv_fuse(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps);
  * (tests/qompiler/circuits/test_qompiler.py:79-82).                                 */
 int qsv_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, void* stream);
 
+/* qsv_fuse with a requested END layout: after the program, logical index bit b sits at physical position
+ * final_pos[b] (a permutation of 0..n_bits-1 that keeps the batch bits; identity = what qsv_fuse delivers).  The
+ * correcting permutation rides on a compute sweep's out-of-place store where the tile allows, else one gate-free
+ * permuting sweep is appended.  A sharded run asks for the layout its next exchange step needs (victim bits parked in
+ * the top positions).  With carry_exchange != 0 the plan's LAST sweep is guaranteed to store out of place, in a kernel
+ * image whose store can fan out over peer buffers: qsv_run_exchange then makes that store the exchange itself.
+ * One-target gate kinds only.  No reference counterpart (the reference has neither layouts nor ranks).           */
+int qsv_fuse_to_layout(qsv_ctx* ctx, int max_tile_bits, const int* final_pos, int carry_exchange, uint64_t* out_sweeps);
+/* qsv_run for a plan built with carry_exchange: every sweep but the last runs locally between `state` and `spare`
+ * (pass both); the last one stores each amplitude straight into the rank that owns it after the exchange "the g_bits
+ * global bits trade places with the top g_bits local bits": the top g_bits of the (permuted) output index select
+ * peer_out[r], this rank's id takes their place in the address there (as in qsv_permute_exchange).  peer_out[r] =
+ * peer-mapped device address of rank r's destination buffer (peer_out[rank] = this rank's own).  The caller brackets
+ * the call with barriers across the ranks: nobody may still read its destination buffer, and all stores must have
+ * landed before anyone uses the result.  ONE kernel computes the segment's last gates and performs the collective.  */
+int qsv_run_exchange(qsv_ctx* ctx, void* state, void* spare, void* const* peer_out, int g_bits, int rank, void* stream);
+
 /* Shape of the fused plan built by qsv_fuse: number of fused sweeps and how many of them store out of place (each of
  * those makes qsv_run's result change buffers once).  Ranks of a sharded run use it to agree, before the first run, on
  * which of their two buffers will hold a segment's result.  No reference counterpart.                          */

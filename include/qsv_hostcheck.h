@@ -28,6 +28,13 @@ extern "C" {
 int qsv_hostcheck_fused(int dtype, int n_bits, const qsv_gate_t* gates, uint64_t n_gates, const double* pool, uint64_t pool_elems,
                         int max_tile_bits, void* state, uint64_t* out_sweeps, uint64_t* out_fft_sweeps, char* err, uint64_t err_len);
 
+/* The same with a requested end layout (qsv_fuse_to_layout): the result is left with logical bit b at physical position
+ * final_pos[b]; carry_exchange != 0 additionally demands that the last sweep can carry an exchange (out-of-place store
+ * in a cp.async image) and fails otherwise.  final_pos == NULL: canonical layout.                                    */
+int qsv_hostcheck_fused_layout(int dtype, int n_bits, const qsv_gate_t* gates, uint64_t n_gates, const double* pool, uint64_t pool_elems,
+                               int max_tile_bits, const int* final_pos, int carry_exchange, void* state, uint64_t* out_sweeps,
+                               uint64_t* out_fft_sweeps, char* err, uint64_t err_len);
+
 #ifdef __cplusplus
 }
 #endif

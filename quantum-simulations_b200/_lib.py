@@ -44,6 +44,8 @@ _SIGNATURES = {
     "qsv_upload_program": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]),
     "qsv_fuse": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]),
     "qsv_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.c_void_p]),
+    "qsv_fuse_to_layout": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]),
+    "qsv_run_exchange": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "qsv_plan_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "qsv_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "qsv_get_sweep_profile": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int, C.POINTER(C.c_int)]),

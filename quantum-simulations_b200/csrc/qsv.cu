@@ -84,7 +84,8 @@ __global__ void __launch_bounds__(256) k_gate1(typename cplx_of<R>::type* __rest
 // K1 for a LOW target bit (below the warp width), uncontrolled: every lane loads ONE amplitude (a warp reads 512 contiguous
 // bytes), gets its partner from lane ^ 2^t with warp shuffles, and writes its own output -- the "warp-shuffle exchange for
 // low-index target qubits".  k_gate1 handles the same gates by giving each thread both amplitudes of a pair (32 contiguous
-// bytes per thread for t = 0); which one is faster is an A/B kept in profiles/ (QSV_SHFL=1 selects this kernel).
+// bytes per thread for t = 0); measured 1-3 % slower (profiles/r2_ab_shuffle.txt), so this kernel is the default for these
+// gates and QSV_NO_SHFL=1 selects the pair kernel.
 template <typename R, int U>
 __global__ void __launch_bounds__(256) k_gate1_shfl(typename cplx_of<R>::type* __restrict__ st, uint64_t namps, int t, Mat2 mat) {
     typedef typename cplx_of<R>::type C;
@@ -472,7 +473,7 @@ static int launch_gate1(qsv_ctx* ctx, void* state, int n_bits, const qsv_gate_t*
         k_phase1<R, U><<<(unsigned)blocks, 256, 0, s>>>((C*)state, namps, ins, mat[6], mat[7]);
         ctx->stats.amp_bytes += 2 * namps * sizeof(C);
     } else {
-        static const bool use_shfl = getenv("QSV_SHFL") != nullptr;  // measured no faster than the pair kernel (profiles/r2_ab_shuffle.txt)
+        static const bool use_shfl = getenv("QSV_NO_SHFL") == nullptr;  // measured 1-3 % faster than the pair kernel (profiles/r2_ab_shuffle.txt)
         if (use_shfl && kind == QSV_DENSE1 && g->ctrl_mask == 0 && g->target_bits[0] < 5 && n_bits >= 5) {
             const uint64_t namps = 1ull << n_bits;
             const uint64_t blocks = (namps + 256 * U - 1) / (256 * U);
@@ -773,6 +774,41 @@ int qsv_fuse(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
         if (rc != QSV_E_UNSUPPORTED) return rc;
     }
     return sweep_plan_build(ctx, max_tile_bits, out_sweeps);
+}
+
+int qsv_fuse_to_layout(qsv_ctx* ctx, int max_tile_bits, const int* final_pos, int carry_exchange, uint64_t* out_sweeps) {
+    if (!ctx) return QSV_E_INVALID;
+    if (!ctx->has_program) return qsv_fail(ctx, QSV_E_NOPROGRAM, "qsv_fuse_to_layout before qsv_upload_program");
+    if (!final_pos) return qsv_fail(ctx, QSV_E_INVALID, "final_pos is NULL");
+    uint64_t seen = 0;
+    for (int b = 0; b < ctx->prog_bits; ++b) {
+        if (final_pos[b] < 0 || final_pos[b] >= ctx->prog_bits || (seen & (1ull << final_pos[b])))
+            return qsv_fail(ctx, QSV_E_INVALID, "final_pos is not a permutation of the index bits");
+        seen |= 1ull << final_pos[b];
+        if (b < ctx->prog_batch_bits && final_pos[b] != b) return qsv_fail(ctx, QSV_E_INVALID, "batch bits cannot move");
+    }
+    for (const qsv_gate_t& g : ctx->gates)
+        if (g.kind == QSV_ROWS2 || g.kind == QSV_DENSEK)
+            return qsv_fail(ctx, QSV_E_UNSUPPORTED, "unsupported: a requested layout needs a program of one-target gates");
+    QSV_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ctx->rows_plan) { rowslab_free(ctx->rows_plan); ctx->rows_plan = nullptr; }
+    return sweep_plan_build(ctx, max_tile_bits, out_sweeps, final_pos, carry_exchange != 0);
+}
+
+int qsv_run_exchange(qsv_ctx* ctx, void* state, void* spare, void* const* peer_out, int g_bits, int rank, void* stream) {
+    if (!ctx) return QSV_E_INVALID;
+    if (!ctx->plan) return qsv_fail(ctx, QSV_E_NOPROGRAM, "qsv_run_exchange before qsv_fuse_to_layout");
+    if (!state || !peer_out) return qsv_fail(ctx, QSV_E_INVALID, "NULL argument");
+    if (g_bits < 1 || g_bits > 3) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "g_bits=%d: 2, 4 or 8 ranks are supported", g_bits);
+    if (rank < 0 || rank >= (1 << g_bits)) return qsv_fail(ctx, QSV_E_INVALID, "rank %d out of range", rank);
+    uint64_t peers[8] = {0};
+    for (int i = 0; i < (1 << g_bits); ++i) {
+        if (!peer_out[i]) return qsv_fail(ctx, QSV_E_INVALID, "peer buffer %d is NULL", i);
+        peers[i] = (uint64_t)peer_out[i];
+    }
+    QSV_CUDA(ctx, cudaSetDevice(ctx->device));
+    int flag = 0;
+    return sweep_plan_run(ctx, state, spare, &flag, (cudaStream_t)stream, g_bits, rank, peers);
 }
 
 int qsv_plan_info(qsv_ctx* ctx, uint64_t* out_sweeps, uint64_t* out_of_place_sweeps) {

@@ -93,8 +93,10 @@ static inline size_t amp_size(int dtype) { return dtype == QSV_C128 ? 16 : 8; }
 
 // implemented in qsv_sweep.cu
 void sweep_plan_free(SweepPlan* p);
-int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps);
-int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream);
+int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps, const int* final_pos = nullptr, bool carry_exchange = false);
+// xg > 0: the plan's last sweep stores into the peers' buffers (peers[0 .. 2^xg)), see SweepDesc::xg
+int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream, int xg = 0, int xrank = 0,
+                   const uint64_t* peers = nullptr);
 int sweep_plan_collect_profile(qsv_ctx* ctx, float* ms, int cap, int* n_out);
 void sweep_plan_count(const SweepPlan* plan, uint64_t* sweeps, uint64_t* out_of_place);
 // implemented in qsv_rows.cu

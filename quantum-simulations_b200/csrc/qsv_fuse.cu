@@ -77,11 +77,18 @@ struct Builder {
     int rb = RB;
     bool tma_swizzle = false;          // tile slots follow the TMA engine's 128-byte swizzle instead of swz()
     bool allow8 = true;                // (sweep_plan_build_host: complex128, QSV_NO_FFT8 unset)
+    // Layout the plan must END in: logical bit b at physical position final_pos[b] (identity = canonical).  A sharded run
+    // asks for the layout its next exchange step needs, so that the correcting permutation rides on the last compute
+    // sweep's store instead of costing a sweep of its own.  carry_exchange: the plan's last sweep must store out of place
+    // (its store becomes the exchange: it writes into the peers' buffers) and must run in an image that can do that.
+    int final_pos[64];
+    bool carry_exchange = false;
+    bool last_flush = false;
     uint32_t sw(uint32_t l) const { return tma_swizzle ? swz128(l) : swz(l); }
 
     Builder(qsv_ctx* c, SweepPlan* p, int n_, int k_) : ctx(c), plan(p), n(n_), k(k_) {
         c_low = (k < n) ? std::min(4, k - 1) : 0;
-        for (int b = 0; b < 64; ++b) pos[b] = b;
+        for (int b = 0; b < 64; ++b) pos[b] = final_pos[b] = b;
         find_swaps();
     }
 
@@ -185,12 +192,12 @@ struct Builder {
         for (int b = 0; b < n; ++b) tau[b] = b;
         for (auto& ev : swaps)
             if (ev.first >= from) std::swap(tau[ev.a], tau[ev.b]);
-        // at the end logical b would live at pos[tau[b]]; we want it at b
+        // at the end logical b would live at pos[tau[b]]; we want it at final_pos[b] (canonical: b)
         P.assign(n, 0);
         bool any = false;
         for (int b = 0; b < n; ++b) {
-            P[pos[tau[b]]] = b;
-            any |= pos[tau[b]] != b;
+            P[pos[tau[b]]] = final_pos[b];
+            any |= pos[tau[b]] != final_pos[b];
         }
         return any;
     }
@@ -200,9 +207,9 @@ struct Builder {
     }
 
     // stand-alone permuting sweep (no gates) that restores the canonical layout
-    int restore_layout() {
+    int restore_layout(bool even_if_identity = false) {
         std::vector<int> P;
-        if (!pending_permutation((size_t)-1, P)) return QSV_OK;   // only relabels already made count
+        if (!pending_permutation((size_t)-1, P) && !even_if_identity) return QSV_OK;   // only relabels already made count
         uint64_t need = forced_mask();
         for (int p = 0; p < n; ++p)
             if (P[p] < c_low) need |= 1ull << p;
@@ -975,7 +982,8 @@ struct Builder {
                 if (pg[gi].kind != QSV_DIAG1) seen |= 1ull << pg[gi].target_bits[0];
             n_t = __builtin_popcountll(seen);
         }
-        const bool try8 = allow8 && k < n && k >= 9 && k <= 11 && n_t >= 1 && n_t <= 6 && n_t != 4;
+        // (a sweep whose store carries an exchange fans out over several peers: the cp.async images do that, the TMA store does not)
+        const bool try8 = allow8 && !(last_flush && carry_exchange) && k < n && k >= 9 && k <= 11 && n_t >= 1 && n_t <= 6 && n_t != 4;
         if (try8) {
             const size_t steps0 = plan->steps.size(), aux0 = plan->aux.size();
             const uint64_t targets0 = cur_targets;
@@ -1004,7 +1012,7 @@ struct Builder {
         // when the tile also holds the bits that become the low (coalescing) bits of the output.
         std::vector<int> P;
         bool fold = false;
-        if (pending_permutation(next_gate, P)) {
+        if (pending_permutation(next_gate, P) || (last_flush && carry_exchange)) {
             uint64_t need = cur_targets | forced_mask();
             for (int p = 0; p < n; ++p)
                 if (P[p] < c_low) need |= 1ull << p;
@@ -1129,7 +1137,7 @@ struct Builder {
 
 }  // namespace
 
-int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan) {
+int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan, const int* final_pos, bool carry_exchange) {
     const int n = ctx->prog_bits;
     if (n < RB) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "unsupported: fused sweeps need at least %d index bits (have %d)", RB, n);
     // default tile: the whole state when it fits, else 2^11 amplitudes (32 KB): measured best on B200 -- three
@@ -1150,13 +1158,22 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan)
         b.target_cap = cap;
         static const bool no8 = getenv("QSV_NO_FFT8") != nullptr;  // A/B aid: keep every launch in the cp.async images
         b.allow8 = ctx->dtype == QSV_C128 && !no8;
+        if (final_pos)
+            for (int q = 0; q < n; ++q) b.final_pos[q] = final_pos[q];
+        b.carry_exchange = carry_exchange;
         int rc = QSV_OK;
         for (size_t i = 0; i < ctx->gates.size() && !rc; ++i) rc = b.add_gate(i);
         if (!rc) {
             b.next_gate = ctx->gates.size();
+            b.last_flush = true;
             rc = b.flush();
         }
-        if (!rc) rc = b.restore_layout();
+        if (!rc) {
+            // the exchange rides on an out-of-place store: if the last sweep is not one, a gate-free permuting sweep is added
+            const bool last_ok = !plan->steps.empty() && plan->steps.back().fused && plan->steps.back().out_of_place &&
+                                 plan->steps.back().img != IMG_FFT8;
+            rc = b.restore_layout(carry_exchange && !last_ok);
+        }
         if (rc) {
             delete plan;
             return rc;

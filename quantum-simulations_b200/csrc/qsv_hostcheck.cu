@@ -271,9 +271,20 @@ static int hostcheck_run(qsv_ctx* ctx, SweepPlan* plan, void* state, uint64_t* o
     return QSV_OK;
 }
 
+extern "C" int qsv_hostcheck_fused_layout(int dtype, int n_bits, const qsv_gate_t* gates, uint64_t n_gates, const double* pool,
+                                          uint64_t pool_elems, int max_tile_bits, const int* final_pos, int carry_exchange, void* state,
+                                          uint64_t* out_sweeps, uint64_t* out_fft_sweeps, char* err, uint64_t err_len);
+
 extern "C" int qsv_hostcheck_fused(int dtype, int n_bits, const qsv_gate_t* gates, uint64_t n_gates, const double* pool, uint64_t pool_elems,
                                    int max_tile_bits, void* state, uint64_t* out_sweeps, uint64_t* out_fft_sweeps, char* err,
                                    uint64_t err_len) {
+    return qsv_hostcheck_fused_layout(dtype, n_bits, gates, n_gates, pool, pool_elems, max_tile_bits, nullptr, 0, state, out_sweeps,
+                                      out_fft_sweeps, err, err_len);
+}
+
+extern "C" int qsv_hostcheck_fused_layout(int dtype, int n_bits, const qsv_gate_t* gates, uint64_t n_gates, const double* pool,
+                                          uint64_t pool_elems, int max_tile_bits, const int* final_pos, int carry_exchange, void* state,
+                                          uint64_t* out_sweeps, uint64_t* out_fft_sweeps, char* err, uint64_t err_len) {
     qsv_ctx ctx;  // never touches a device
     ctx.dtype = dtype;
     int rc = QSV_OK;
@@ -295,7 +306,9 @@ extern "C" int qsv_hostcheck_fused(int dtype, int n_bits, const qsv_gate_t* gate
         ctx.pool.assign(pool, pool + 2 * pool_elems);
         ctx.prog_bits = n_bits;
         ctx.has_program = true;
-        rc = sweep_plan_build_host(&ctx, max_tile_bits, &plan);
+        rc = sweep_plan_build_host(&ctx, max_tile_bits, &plan, final_pos, carry_exchange != 0);
+        if (!rc && carry_exchange && (plan->steps.empty() || !plan->steps.back().out_of_place || plan->steps.back().img == IMG_FFT8))
+            rc = qsv_fail(&ctx, QSV_E_INVALID, "hostcheck: the plan's last sweep cannot carry an exchange");
     }
     if (!rc && !state) {
         uint64_t sweeps = 0, fft = 0;

@@ -165,7 +165,16 @@ __global__ void __launch_bounds__(MAXT, MINB) k_sweep(const typename cplx_of<R>:
                 const uint64_t gb = gbs;
 #pragma unroll
                 for (int i = 0; i < NREG; ++i)
-                    if (i < n_slots) dst[gb | D.st_goff[i]] = tile[t_st_s ^ D.st_soff[i]];  // (exchange sweeps carry no ops and never use this image)
+                    if (i < n_slots) {
+                        const uint64_t y = gb | D.st_goff[i];
+                        if (D.xg) {  // the store IS the exchange: top xg bits of the output index -> destination rank
+                            const int sh = D.n_bits - D.xg;
+                            C* pd = reinterpret_cast<C*>(D.peer[y >> sh]);
+                            pd[((uint64_t)D.xrank << sh) | (y & ((1ull << sh) - 1ull))] = tile[t_st_s ^ D.st_soff[i]];
+                        } else {
+                            dst[y] = tile[t_st_s ^ D.st_soff[i]];
+                        }
+                    }
             }
         } else {
         C v[NREG];
@@ -272,10 +281,10 @@ static int sweep_set_smem_attr(qsv_ctx* ctx, int k);
 int sweep8_prepare(qsv_ctx* ctx, int k);
 int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const double* d_aux, const PlanStep& st, cudaStream_t stream);
 
-int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps) {
+int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps, const int* final_pos, bool carry_exchange) {
     SweepPlan* plan = nullptr;
     {
-        int rc = sweep_plan_build_host(ctx, max_tile_bits, &plan);
+        int rc = sweep_plan_build_host(ctx, max_tile_bits, &plan, final_pos, carry_exchange);
         if (rc) return rc;
     }
     const int k = plan->k;
@@ -386,12 +395,26 @@ int sweep_permute_run(qsv_ctx* ctx, const void* in, void* out, int n_bits, const
     return QSV_OK;
 }
 
-int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream) {
+int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare, cudaStream_t stream, int xg, int xrank,
+                   const uint64_t* peers) {
     SweepPlan* plan = ctx->plan;
     const int n = ctx->prog_bits, k = plan->k;
     void* cur = state;
     void* other = spare;
+    if (xg > 0) {
+        if (plan->steps.empty() || !plan->steps.back().fused || !plan->steps.back().out_of_place || plan->steps.back().img == IMG_FFT8)
+            return qsv_fail(ctx, QSV_E_INVALID, "this plan was not built to carry an exchange (qsv_fuse_to_layout with carry_exchange)");
+    }
     for (auto& st : plan->steps) {
+        const bool carries = xg > 0 && &st == &plan->steps.back();
+        SweepParams* patched = nullptr;
+        if (carries) {
+            // the last sweep's store goes to the peers: same launch, destination table filled in
+            patched = new SweepParams(*st.params);
+            patched->d.xg = xg;
+            patched->d.xrank = xrank;
+            for (int i = 0; i < (1 << xg); ++i) patched->d.peer[i] = peers[i];
+        }
         if (!st.fused) {
             int rc = qsv_apply_planned_single(ctx, cur, st.gate_index, stream);
             if (rc) return rc;
@@ -410,7 +433,8 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
         }
         {
             int rc = st.img == IMG_FFT8 ? sweep8_launch(ctx, n, k, cur, dstp, plan->d_aux, st, stream)
-                                        : sweep_launch(ctx, n, k, cur, dstp, plan->d_aux, *st.params, stream, st.img);
+                                        : sweep_launch(ctx, n, k, cur, dstp, plan->d_aux, patched ? *patched : *st.params, stream, st.img);
+            delete patched;
             if (rc) return rc;
         }
         static const bool sync_each = getenv("QSV_SYNC") != nullptr;  // debugging aid: surface kernel faults at the launch site

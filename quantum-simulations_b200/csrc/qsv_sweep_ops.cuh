@@ -756,5 +756,5 @@ struct SweepPlan {
 
 
 // the fusion pass (qsv_fuse.cu, host only: builds plans without touching a device)
-int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan);
+int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan, const int* final_pos = nullptr, bool carry_exchange = false);
 int sweep_permute_plan_build(qsv_ctx* ctx, int n_bits, const int* perm, int k, SweepPlan* tmp);

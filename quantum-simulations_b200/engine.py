@@ -111,6 +111,20 @@ class Engine:
         check(self.lib.qsv_fuse(self._ctx, max_tile_bits, C.byref(n)), self._ctx)
         return int(n.value)
 
+    def fuse_to_layout(self, final_pos, carry_exchange=False, max_tile_bits: int = 0) -> int:
+        """:meth:`fuse` with a requested end layout (logical bit b -> physical position ``final_pos[b]``)."""
+        n = C.c_uint64(0)
+        p = np.ascontiguousarray(final_pos, dtype=np.int32)
+        check(self.lib.qsv_fuse_to_layout(self._ctx, max_tile_bits, p.ctypes.data_as(C.c_void_p), int(bool(carry_exchange)), C.byref(n)),
+              self._ctx)
+        return int(n.value)
+
+    def run_exchange(self, state, spare, peer_ptrs, g_bits: int, rank: int):
+        """Run a plan built with ``carry_exchange``: its last sweep stores into the peers' buffers."""
+        arr = (C.c_void_p * len(peer_ptrs))(*peer_ptrs)
+        sp = C.c_void_p(spare.data_ptr()) if spare is not None else C.c_void_p()
+        check(self.lib.qsv_run_exchange(self._ctx, C.c_void_p(state.data_ptr()), sp, arr, g_bits, rank, self._stream()), self._ctx)
+
     def plan_info(self):
         """(fused sweeps, out-of-place sweeps) of the plan built by :meth:`fuse`."""
         a, b = C.c_uint64(0), C.c_uint64(0)

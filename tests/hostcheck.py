@@ -46,6 +46,27 @@ def run_fused_on_host(recs, pool, state, n_bits, tile_bits=0, dtype=np.complex12
     return out, int(sweeps.value), int(fft.value)
 
 
+def run_fused_to_layout_on_host(recs, pool, state, n_bits, final_pos, carry_exchange=False, tile_bits=0):
+    """Like run_fused_on_host for a plan with a requested end layout (logical bit b -> physical position final_pos[b])."""
+    _load()
+    lib = C.CDLL(HOSTCHECK_PATH)
+    fn = lib.qsv_hostcheck_fused_layout
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                   C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_char_p, C.c_uint64]
+    recs = np.ascontiguousarray(recs, dtype=_lib.GATE_DTYPE)
+    pool = np.ascontiguousarray(pool, dtype=np.complex128)
+    out = np.ascontiguousarray(state, dtype=np.complex128).reshape(-1).copy()
+    fp = np.ascontiguousarray(final_pos, dtype=np.int32)
+    sweeps, fft = C.c_uint64(0), C.c_uint64(0)
+    err = C.create_string_buffer(512)
+    rc = fn(_lib.QSV_C128, n_bits, recs.ctypes.data, len(recs), pool.ctypes.data if pool.size else None, pool.size, tile_bits,
+            fp.ctypes.data, int(carry_exchange), out.ctypes.data, C.byref(sweeps), C.byref(fft), err, 512)
+    if rc:
+        raise RuntimeError(f"qsv_hostcheck_fused_layout rc={rc}: {err.value.decode()}")
+    return out, int(sweeps.value), int(fft.value)
+
+
 def plan_shape(recs, pool, n_bits, tile_bits=0):
     """(n_sweeps, n_fft_sweeps) of the fused plan for a register of any size -- nothing is executed."""
     fn = _load()

@@ -180,3 +180,36 @@ def test_batched_qft_config3_shape_and_semantics():
     x /= np.linalg.norm(x, axis=0)
     got, _, fft = run_fused_on_host(p.records(b), p.pool(), x.reshape(-1), n + b, 11)
     assert fft >= 1 and np.abs(got.reshape(1 << n, 1 << b) - np.fft.ifft(x, axis=0, norm="ortho")).max() < 1e-12
+
+
+@pytest.mark.parametrize("carry", [False, True])
+@pytest.mark.parametrize("n,tile", [(13, 9), (14, 11), (16, 11)])
+def test_requested_end_layout(n, tile, carry):
+    """qsv_fuse_to_layout: the plan leaves logical bit b at physical position final_pos[b] -- the layout a sharded run's next
+    exchange needs -- whether the permutation rides on a compute sweep or needs a sweep of its own; with carry_exchange the
+    last sweep is an out-of-place one in an image whose store can fan out over peers."""
+    from oracle import sv_oracle as orc
+    from tests.hostcheck import run_fused_to_layout_on_host
+    rng = np.random.default_rng(n * 7 + carry)
+    for case in range(4):
+        prog = qft_program(n) if case == 0 else _fft_like_program(rng, n, ordered=bool(case & 1))
+        final = list(range(n))
+        if case != 3:                                  # park three random bits in the top positions, keep the rest in order
+            victims = sorted(rng.choice(n, size=3, replace=False).tolist())
+            rest = [b for b in range(n) if b not in victims]
+            for i, b in enumerate(rest):
+                final[b] = i
+            for i, b in enumerate(victims):
+                final[b] = n - 3 + i
+        x = rng.standard_normal(1 << n) + 1j * rng.standard_normal(1 << n)
+        x /= np.linalg.norm(x)
+        got, sweeps, _ = run_fused_to_layout_on_host(prog.records(0), prog.pool(), x, n, final, carry, tile)
+        ref = x.copy()
+        orc.run_records(prog.records(0), prog.pool(), ref, n)
+        idx = np.arange(1 << n)
+        phys = np.zeros_like(idx)
+        for b in range(n):
+            phys |= ((idx >> b) & 1) << final[b]
+        want = np.empty_like(ref)
+        want[phys] = ref
+        assert np.abs(got - want).max() < 1e-12, (case, final)

@@ -524,8 +524,9 @@ def test_dela_with_a_state_other_than_ket0(fuse):
 
 
 def test_warp_shuffle_kernel_for_low_target_bits():
-    """QSV_SHFL=1 routes uncontrolled dense gates on index bits 0..4 through k_gate1_shfl (partner amplitude fetched with
-    warp shuffles).  The switch is read once per process, so the run happens in a child process; result against the oracle."""
+    """Uncontrolled dense gates on index bits 0..4 go through k_gate1_shfl (partner amplitude fetched with warp shuffles),
+    QSV_NO_SHFL=1 sends them through the pair kernel.  The switch is read once per process, so both settings run in child
+    processes; results against the oracle."""
     import os
     import subprocess
     import sys
@@ -552,6 +553,7 @@ for dt, tol in ((np.complex128, 1e-10), (np.complex64, 1e-5)):
     assert err < tol * np.abs(ref).max(), err
 print("ok")
 """ % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    env = dict(os.environ, QSV_SHFL="1")
-    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
-    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+    for extra in ({}, {"QSV_NO_SHFL": "1"}):
+        env = dict(os.environ, **extra)
+        out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]

@@ -185,7 +185,7 @@ def test_library_exports_every_declared_symbol():
     # the test-only host check of the fusion pass has its own header and is bound under tests/, not in the package
     hc = open(os.path.join(ROOT, "include", "qsv_hostcheck.h")).read()
     hc_declared = set(re.findall(r"\b(qsv_[a-z0-9_]+)\s*\(", hc))
-    assert hc_declared == {"qsv_hostcheck_fused"}
+    assert hc_declared == {"qsv_hostcheck_fused", "qsv_hostcheck_fused_layout"}
     assert not hasattr(lib, "qsv_hostcheck_fused"), "the host interpreter must not be part of the product library"
     from tests.hostcheck import HOSTCHECK_PATH
     assert hasattr(ctypes.CDLL(HOSTCHECK_PATH), "qsv_hostcheck_fused")
