@@ -508,6 +508,7 @@ def main():
     ap.add_argument("--no-fuse", action="store_true")
     ap.add_argument("--no-check", action="store_true", help="skip the correctness check that follows the timed region")
     ap.add_argument("--no-qft34", action="store_true", help="on 8 GPUs: do not append the QFT-34 (BASELINE config 5) record")
+    ap.add_argument("--no-merge", action="store_true", help="sharded runs: keep park permutation / exchange as sweeps of their own (A/B)")
     ap.add_argument("--restore-layout", action="store_true",
                     help="sharded runs: bring the result back to the canonical layout (one more exchange per QFT) instead of "
                          "reporting the final bit-position table")

@@ -84,6 +84,9 @@ struct Builder {
     int final_pos[64];
     bool carry_exchange = false;
     bool last_flush = false;
+    // With a requested end layout the permutation is folded into the LAST sweep only: the exchange that follows wants it
+    // there, and an early out-of-place sweep would make the segment ping-pong through the buffer the peers store into.
+    bool defer_fold = false;
     uint32_t sw(uint32_t l) const { return tma_swizzle ? swz128(l) : swz(l); }
 
     Builder(qsv_ctx* c, SweepPlan* p, int n_, int k_) : ctx(c), plan(p), n(n_), k(k_) {
@@ -1012,7 +1015,7 @@ struct Builder {
         // when the tile also holds the bits that become the low (coalescing) bits of the output.
         std::vector<int> P;
         bool fold = false;
-        if (pending_permutation(next_gate, P) || (last_flush && carry_exchange)) {
+        if ((!defer_fold || last_flush) && (pending_permutation(next_gate, P) || (last_flush && carry_exchange))) {
             uint64_t need = cur_targets | forced_mask();
             for (int p = 0; p < n; ++p)
                 if (P[p] < c_low) need |= 1ull << p;
@@ -1161,6 +1164,7 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
         if (final_pos)
             for (int q = 0; q < n; ++q) b.final_pos[q] = final_pos[q];
         b.carry_exchange = carry_exchange;
+        b.defer_fold = final_pos != nullptr;
         int rc = QSV_OK;
         for (size_t i = 0; i < ctx->gates.size() && !rc; ++i) rc = b.add_gate(i);
         if (!rc) {

@@ -384,6 +384,24 @@ class SymmExchanger:
         return spare, state
 
 
+def _segment_exchange(self, executor, key, state, spare):
+    """A whole local segment whose LAST sweep is the exchange: that sweep's store writes every amplitude into the rank
+    that owns it afterwards, over peer memory (``qsv_run_exchange``) -- the segment's last gates and the all-to-all are
+    ONE kernel, and no separate pass over the shard is spent on the exchange.  The plan was built so that every earlier
+    sweep works in place: the destination (this rank's ``spare``) is untouched until the peers' stores arrive."""
+    eng, _ = executor.engines[key]
+    peers = self.peers[spare.data_ptr()]
+    hdl = self.handles[spare.data_ptr()]
+    hdl.barrier(channel=0)      # every rank has finished whatever still touched its destination buffer
+    eng.run_exchange(state, spare, peers, self.g, self.rank)
+    hdl.barrier(channel=1)      # every rank's stores have landed
+    self.bytes_sent += state.numel() * state.element_size() * (self.world - 1) // self.world
+    return spare, state
+
+
+SymmExchanger.segment_exchange = _segment_exchange
+
+
 class GpuExecutor:
     """Runs local segments on the CUDA engine; one libqsv context (with its fused plan) per segment."""
 
@@ -394,17 +412,29 @@ class GpuExecutor:
         self.engines = {}
         self.launches = 0
         self.fused_sweeps_per_apply = 0   # fused compute sweeps of all prepared segments together (one apply runs each once)
+        self.sweeps_of = {}               # segment key -> fused sweeps of its plan
         self.copy_back = {}               # segment key -> True: this rank copies the result back to the buffer it started in
 
-    def prepare(self, key, recs, pool, n_loc):
+    def prepare(self, key, recs, pool, n_loc, final_pos=None, carry_exchange=False):
+        """``final_pos`` (logical bit -> physical position): the layout the segment must end in -- the parking permutation
+        of the exchange that follows rides on the segment's last sweep.  ``carry_exchange``: that sweep can store into the
+        peers' buffers.  Returns the parity of the plan's out-of-place sweeps (1 = the result changes buffers)."""
         from .engine import Engine
         eng = Engine(self.device, np.complex128)
         eng.upload_records(recs, pool, n_loc, 0)
         fused = False
         flips = 0
-        if self.fuse and len(recs):
+        if self.fuse and final_pos is not None:
+            self.sweeps_of[key] = int(eng.fuse_to_layout(final_pos, carry_exchange, self.tile_bits))
+            self.fused_sweeps_per_apply += self.sweeps_of[key]
+            fused = True
+            n_sw, n_oop = eng.plan_info()
+            assert n_oop == 1, "a segment that ends in a requested layout stores out of place exactly once, in its last sweep"
+            flips = 1
+        elif self.fuse and len(recs):
             # (no per-gate downgrade here: a segment the fusion pass refuses is a planning error at these sizes)
-            self.fused_sweeps_per_apply += int(eng.fuse(self.tile_bits))
+            self.sweeps_of[key] = int(eng.fuse(self.tile_bits))
+            self.fused_sweeps_per_apply += self.sweeps_of[key]
             fused = True
             flips = eng.plan_info()[1] & 1
         self.engines[key] = (eng, fused)
@@ -462,7 +492,7 @@ class ShardedCircuit:
     ``final_where`` (logical bit -> physical position, global positions last): QFT then needs two exchange steps
     instead of three -- its final SWAP layer becomes output ordering."""
 
-    def __init__(self, recs, pool, n_bits, rank, world, executor, exchanger, restore=True, all_reduce_min=None):
+    def __init__(self, recs, pool, n_bits, rank, world, executor, exchanger, restore=True, all_reduce_min=None, merge_exchanges=True):
         g = world.bit_length() - 1
         assert 1 << g == world, "world size must be a power of two"
         self.plan = plan_sharded(recs, n_bits, g, restore=restore)
@@ -474,14 +504,37 @@ class ShardedCircuit:
         li = 0
         self._keys = []
         flips = []
-        for s in self.plan.steps:
+        # A local segment followed by (park permutation,) exchange: the permutation rides on the segment's last sweep, and
+        # with the peer-memory engine that sweep's store IS the exchange.  self._merged[k] = number of plan steps the
+        # segment at step index k swallows (0: nothing merged).
+        self._merged = {}
+        can_layout = merge_exchanges and hasattr(executor, "agree_on_buffers") and getattr(executor, "fuse", False)
+        steps = self.plan.steps
+        for k, s in enumerate(steps):
             if s[0] == "local":
                 lrecs, lpool = localize_records(recs, pool, s[1], self.plan.where_at[li], self.n_loc, rank)
-                flips.append(int(executor.prepare(li, lrecs, lpool, self.n_loc) or 0))
+                final_pos = None
+                if can_layout and k + 1 < len(steps):
+                    if steps[k + 1][0] == "permute" and k + 2 < len(steps) and steps[k + 2][0] == "xall":
+                        final_pos, swallowed = list(steps[k + 1][1]), (2 if hasattr(exchanger, "segment_exchange") else 1)
+                    elif steps[k + 1][0] == "xall" and hasattr(exchanger, "segment_exchange"):
+                        final_pos, swallowed = list(range(self.n_loc)), 1
+                if final_pos is not None:
+                    carry = hasattr(exchanger, "segment_exchange")
+                    flips.append(int(executor.prepare(li, lrecs, lpool, self.n_loc, final_pos=final_pos, carry_exchange=carry)))
+                    self._merged[k] = (swallowed, carry)
+                else:
+                    flips.append(int(executor.prepare(li, lrecs, lpool, self.n_loc) or 0))
                 self._keys.append(li)
                 li += 1
         if all_reduce_min is not None and hasattr(executor, "agree_on_buffers"):
             executor.agree_on_buffers(self._keys, flips, all_reduce_min)
+        # sweeps whose time shows up under "local" in a per-step split (the exchange-carrying segments are timed as a whole)
+        carrying = {self._keys[i] for i, k_ in enumerate(k2 for k2, s2 in enumerate(steps) if s2[0] == "local")
+                    if self._merged.get(k_, (0, False))[1]}
+        so = getattr(executor, "sweeps_of", {})
+        self.plain_local_sweeps = sum(v for key, v in so.items() if key not in carrying)
+        self.carrying_sweeps = sum(v for key, v in so.items() if key in carrying)
 
     def apply(self, state, spare, timers=None):
         """Returns (state, spare) -- the buffers may have traded places.  ``timers`` (a list) collects one
@@ -492,7 +545,25 @@ class ShardedCircuit:
         k = 0
         while k < len(steps):
             s = steps[k]
+            merged = self._merged.get(k) if s[0] == "local" else None
             k += 1
+            if merged:
+                swallowed, carry = merged
+                if timers is not None:
+                    import torch
+                    e0 = torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                if carry:      # compute + exchange in one kernel (peer stores)
+                    state, spare = self.exchanger.segment_exchange(self.executor, self._keys[li], state, spare)
+                else:          # the parking permutation rode on the segment's last sweep; the exchange itself follows
+                    state, spare = self.executor.run_segment(self._keys[li], state, spare)
+                li += 1
+                k += swallowed
+                if timers is not None:
+                    e1 = torch.cuda.Event(enable_timing=True)
+                    e1.record()
+                    timers.append(("local+xall" if carry else "local", e0, e1))
+                continue
             if fused_x and s[0] in ("permute", "xall"):
                 # (local permutation, exchange) or a bare exchange -> one kernel storing into the peers' buffers
                 if s[0] == "permute" and k < len(steps) and steps[k][0] == "xall":
@@ -581,7 +652,8 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
         return [int(v) for v in t.tolist()][:len(values)]
 
     restore = bool(getattr(args, "restore_layout", False))
-    circ = ShardedCircuit(recs, pool, n, rank, world, execu, exch, restore=restore, all_reduce_min=all_reduce_min)
+    circ = ShardedCircuit(recs, pool, n, rank, world, execu, exch, restore=restore, all_reduce_min=all_reduce_min,
+                          merge_exchanges=not getattr(args, "no_merge", False))
     for _ in range(warmup):
         state, spare = circ.apply(state, spare)
     torch.cuda.synchronize()
@@ -614,8 +686,8 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
     split = {}
     for kind, a, b in timers:
         split[kind] = split.get(kind, 0.0) + a.elapsed_time(b)
-    sp_t = torch.tensor([split.get("local", 0.0), split.get("permute", 0.0), split.get("xall", 0.0) + split.get("exchange", 0.0)],
-                        device=dev, dtype=torch.float64)
+    sp_t = torch.tensor([split.get("local", 0.0), split.get("permute", 0.0), split.get("xall", 0.0) + split.get("exchange", 0.0),
+                         split.get("local+xall", 0.0)], device=dev, dtype=torch.float64)
     dist.all_reduce(sp_t, op=dist.ReduceOp.MAX)
     # ---- correctness at this size, outside the timed region: QFT of a basis state against the closed form on every
     # amplitude of every shard (the layout the run ends in is read through the plan's bit-position table), plus the norm
@@ -708,13 +780,13 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
         # the local compute sweeps on their own (rank 0's plan, the slowest rank's time): what the north-star target
         # "fraction of HBM bandwidth per local-gate sweep" is about -- the aggregate figure below includes exchange time
         local_roof = None
-        n_loc_sweeps = int(getattr(execu, "fused_sweeps_per_apply", 0))
+        n_loc_sweeps = int(getattr(circ, "plain_local_sweeps", 0))
         if n_loc_sweeps and float(sp_t[0]) > 0:
             ach = n_loc_sweeps * 2 * amps * 16 / (float(sp_t[0]) * 1e-3) / 1e9
             local_roof = {"bound": "hbm", "kernel": "k_sweep8 / k_sweep, local compute sweeps of one step", "sweeps_per_step": n_loc_sweeps,
                           "ms_per_step": float(sp_t[0]), "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                           "frac_of_nominal_8TBps": ach / 8000.0}
-        x_ms = float(sp_t[2])
+        x_ms = float(sp_t[2]) + float(sp_t[3])   # (segments whose last sweep is the exchange count whole: a lower bound on the rate)
         sent = float(tot[2]) / world / max(1, steps)
         rec = {"metric": "gates_per_sec", "value": steps * circ.n_gates / sec, "unit": "gates/s", "n_gpus": world,
                "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True,
@@ -722,6 +794,7 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
                "config": B.workload_config(n, circ.n_gates),
                "impl_config": {"sharding": f"top {g} qubits over {world} GPUs", "exchanges_per_step": n_ex, "exchange": exch_kind,
                                "local_amplitudes": amps, "restore_layout": restore, "final_bit_positions": circ.final_where,
+                               "exchange_rides_on_last_sweep": bool(circ._merged),
                                "l2": "local shard far larger than the 126 MB L2" if amps * 16 > (1 << 28) else "local shard fits L2"},
                "amp_GBps": amp_gbps, "hbm_frac_of_measured": amp_gbps / (peak * world),
                "hbm_frac_of_nominal_8TBps": amp_gbps / (8000.0 * world),
@@ -733,7 +806,9 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
                           "achieved_GBps_per_direction_per_gpu": sent / (x_ms * 1e-3) / 1e9 if x_ms > 0 else None,
                           "peak_GBps": 770.0, "peak_source": "measured peer copy per direction (B200_PROFILING.md); nominal 900",
                           "frac": (sent / (x_ms * 1e-3) / 1e9 / 770.0) if x_ms > 0 else None},
-               "ms_split_one_step": {"local_sweeps": float(sp_t[0]), "local_permutes": float(sp_t[1]), "exchanges": x_ms},
+               "ms_split_one_step": {"local_sweeps": float(sp_t[0]), "local_permutes": float(sp_t[1]), "exchanges": float(sp_t[2]),
+                                     "segments_whose_last_sweep_is_the_exchange": float(sp_t[3]),
+                                     "sweeps_in_those_segments": int(getattr(circ, "carrying_sweeps", 0))},
                "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(tot[1]), "clocks": clocks,
                "check": check, "max_abs_err": check["max_abs_err"] if check else None}
     del state, spare, circ, execu, exch
