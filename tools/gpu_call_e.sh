@@ -10,8 +10,9 @@ T="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 1
 timeout 600 $T bench.py --gpus 2 --steps 5 --warmup 3 > $O/r2e_bench_2gpu.json 2> $O/r2e_bench_2gpu.err; echo "rc=$?"
 timeout 600 $T bench.py --gpus 2 --steps 5 --warmup 3 --exchange nccl --e2e-steps 0 > $O/r2e_bench_2gpu_nccl.json 2> $O/r2e_bench_2gpu_nccl.err; echo "rc=$?"
 timeout 600 $T bench.py --gpus 2 --steps 5 --warmup 3 --restore-layout --e2e-steps 0 > $O/r2e_bench_2gpu_restore.json 2> $O/r2e_bench_2gpu_restore.err; echo "rc=$?"
+timeout 600 $T bench.py --gpus 2 --steps 5 --warmup 3 --no-merge --e2e-steps 0 > $O/r2e_bench_2gpu_nomerge.json 2> $O/r2e_bench_2gpu_nomerge.err; echo "rc=$?"
 timeout 300 $T bench.py --impl reference --gpus 2 --steps 2 --warmup 1 > $O/r2e_bench_ref_2gpu.json 2> $O/r2e_bench_ref_2gpu.err; echo "rc=$?"
-for f in 2gpu 2gpu_nccl 2gpu_restore; do python - <<PY
+for f in 2gpu 2gpu_nccl 2gpu_restore 2gpu_nomerge; do python - <<PY
 import json
 try:
     d=json.loads(open("$O/r2e_bench_$f.json").read().strip().splitlines()[-1])
