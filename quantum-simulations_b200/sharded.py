@@ -610,10 +610,11 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
     # exchange engine: the fused peer-memory kernel when torch symmetric memory works here, else NCCL all-to-all
     exch = None
     exch_kind = "nccl all_to_all"
-    # measured (profiles/README.md): direct peer stores beat NCCL on 2 GPUs (45.8 vs 60.7 ms QFT-30), tie on 4 and
-    # lose on 8 (390 vs 656 GB/s per direction per GPU), so "auto" takes the direct engine up to 4 ranks only
+    # measured in round 2 (profiles/r2e_*, r2g_*): with the exchange riding on a compute sweep the peer-memory engine beats
+    # NCCL at every world size on QFT-30 (25.6 / 16.0 / 9.3 ms against 38.8 / 20.1 / 11.2 on 2 / 4 / 8 GPUs)
     want = getattr(args, "exchange", "auto")
-    if want == "fused" or (want == "auto" and world <= 4):
+    auto_fused = world <= 4 or amps <= int(os.environ.get("QSV_FUSED_MAX_AMPS", str(1 << 62)))
+    if want == "fused" or (want == "auto" and auto_fused):
         try:
             exch = SymmExchanger(rank, world, amps, torch.device(dev))
             exch_kind = "fused permute+exchange kernel over peer memory (torch symmetric memory)"
