@@ -16,8 +16,8 @@
 // share a row.  The host therefore LEVELS the ops -- level(op) = 1 + max(level of the last op on either of its rows) -- and
 // sorts them by level (stable).  All ops of a level touch pairwise disjoint rows, so a CTA of up to 1024 threads applies
 // them at once, one (op, column) pair per thread, with ONE CTA barrier per level; for the Givens QR stream of a 1024 x 1024
-// unitary that is ~3 000 levels of ~175 ops instead of 523 776 sequential ops.  The ops of the next level are fetched into
-// registers before the barrier, so their L2 latency hides behind the current level's arithmetic.
+// unitary that is ~2 000 levels of ~256 ops instead of 523 776 sequential ops.  The ops of the next level are staged into
+// shared memory with cp.async while the current level computes.
 #include <algorithm>
 
 #include "qsv_common.cuh"
@@ -44,33 +44,32 @@ struct RowSlabPlan {
     }
 };
 
+// Ops of one level are contiguous in the sorted stream; the ops of level l+1 are copied into a shared-memory staging buffer
+// with cp.async while level l computes (two buffers), so that no pass of a level waits on L2 and no op sits in registers.
+#define ROWLEVEL_STAGE_OPS 512   // ops per staging buffer (40 KB); wider levels (never seen for Givens streams) read the rest from L2
+
 template <typename R>
 __global__ void __launch_bounds__(1024, 1) k_rowlevels(typename cplx_of<R>::type* __restrict__ st, uint64_t dim, uint64_t batch, int cols_log2,
                                                       const RowOp* __restrict__ ops, const uint32_t* __restrict__ level_start,
                                                       uint32_t n_levels) {
     typedef typename cplx_of<R>::type C;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    C* slab = reinterpret_cast<C*>(smem_raw);  // [dim][cols]
+    RowOp* stage = reinterpret_cast<RowOp*>(smem_raw);                                        // [2][ROWLEVEL_STAGE_OPS]
+    C* slab = reinterpret_cast<C*>(smem_raw + 2 * ROWLEVEL_STAGE_OPS * sizeof(RowOp));        // [dim][cols]
     const uint32_t tid = threadIdx.x, T = blockDim.x;
     const uint32_t cols = 1u << cols_log2, cmask = cols - 1u;
     const uint64_t col0 = (uint64_t)blockIdx.x << cols_log2;
     const uint64_t slab_amps = dim << cols_log2;
     for (uint64_t i = tid; i < slab_amps; i += T) slab[i] = st[(i >> cols_log2) * batch + col0 + (i & cmask)];
-    // one (op, column) item per thread and level in the common case; the first item of the NEXT level is fetched early
-    uint32_t s = n_levels ? level_start[0] : 0, e = n_levels ? level_start[1] : 0;
-    uint32_t s2 = e, e2 = n_levels > 1 ? level_start[2] : e;
-    RowOp op;
-    bool have = false;
-    auto fetch = [&](uint32_t first, uint32_t last, RowOp& o) {
-        const uint32_t idx = first + (tid >> cols_log2);
-        if (idx < last) {
-            const uint4* p = reinterpret_cast<const uint4*>(ops + idx);
-            uint4* q = reinterpret_cast<uint4*>(&o);
-#pragma unroll
-            for (int w = 0; w < 5; ++w) q[w] = __ldg(p + w);
-            return true;
+    auto stage_level = [&](uint32_t first, uint32_t last, int buf) {  // all threads: 16-byte pieces of the level's op records
+        const uint32_t n = min(last - first, (uint32_t)ROWLEVEL_STAGE_OPS);
+        const char* src = reinterpret_cast<const char*>(ops + first);
+        char* dst = reinterpret_cast<char*>(stage + buf * ROWLEVEL_STAGE_OPS);
+        for (uint32_t b = tid * 16u; b < n * (uint32_t)sizeof(RowOp); b += T * 16u) {
+            const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst + b);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(src + b));
         }
-        return false;
+        asm volatile("cp.async.commit_group;\n" ::);
     };
     auto apply = [&](const RowOp& o, uint32_t col) {
         C* p0 = slab + ((uint64_t)o.r0 << cols_log2) + col;
@@ -86,26 +85,22 @@ __global__ void __launch_bounds__(1024, 1) k_rowlevels(typename cplx_of<R>::type
             *p1 = cfma(m11, a1, cmul(m10, a0));
         }
     };
-    have = fetch(s, e, op);
-    __syncthreads();
+    uint32_t s = n_levels ? level_start[0] : 0, e = n_levels ? level_start[1] : 0;
+    if (n_levels) stage_level(s, e, 0);
     const uint32_t per_pass = T >> cols_log2;  // ops one pass of the CTA covers
+    const uint32_t my_op = tid >> cols_log2, my_col = tid & cmask;
     for (uint32_t l = 0; l < n_levels; ++l) {
-        RowOp nxt;
-        const bool have_next = (l + 1 < n_levels) && fetch(s2, e2, nxt);
-        const uint32_t e3 = (l + 2 < n_levels) ? level_start[l + 3] : e2;
-        if (have) apply(op, tid & cmask);
-        for (uint32_t first = s + per_pass; first < e; first += per_pass) {  // (levels wider than the CTA: rare)
-            RowOp more;
-            if (fetch(first, e, more)) apply(more, tid & cmask);
-        }
-        __syncthreads();
+        const uint32_t s2 = e, e2 = level_start[l + 2];   // (two padding entries follow the last level)
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        __syncthreads();   // level l's ops are staged; level l-1's row updates are visible; the other staging buffer is free
+        if (l + 1 < n_levels) stage_level(s2, e2, (l + 1) & 1);
+        const RowOp* cur = stage + (l & 1) * ROWLEVEL_STAGE_OPS;
+        const uint32_t n = e - s;
+        for (uint32_t i = my_op; i < n; i += per_pass) apply(i < ROWLEVEL_STAGE_OPS ? cur[i] : ops[s + i], my_col);
         s = s2;
         e = e2;
-        s2 = e2;
-        e2 = e3;
-        op = nxt;
-        have = have_next;
     }
+    __syncthreads();
     for (uint64_t i = tid; i < slab_amps; i += T) st[(i >> cols_log2) * batch + col0 + (i & cmask)] = slab[i];
 }
 
@@ -122,7 +117,7 @@ int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out) {
     const uint64_t qmask = (dim - 1) << b;
     // columns per CTA: as many as fit next to the op buffers in ~200 KB, at most a warp and at most the batch
     const size_t amp = amp_size(ctx->dtype);
-    const size_t budget = 200 * 1024;
+    const size_t budget = 224 * 1024 - 2 * ROWLEVEL_STAGE_OPS * sizeof(RowOp);
     uint64_t cols = budget / (dim * amp);
     if (cols < 1) return QSV_E_UNSUPPORTED;
     cols = std::min<uint64_t>(std::min<uint64_t>(cols, 32), batch);
@@ -221,7 +216,7 @@ int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out) {
             return qsv_fail(ctx, QSV_E_CUDA, "uploading the row-op stream failed: %s", cudaGetErrorString(e));
         }
     }
-    const int smem = (int)(dim * cols * amp);
+    const int smem = (int)(2 * ROWLEVEL_STAGE_OPS * sizeof(RowOp) + dim * cols * amp);
     cudaError_t e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_rowlevels<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
                                            : cudaFuncSetAttribute(k_rowlevels<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
@@ -234,7 +229,7 @@ int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out) {
 
 int rowslab_run(qsv_ctx* ctx, RowSlabPlan* plan, void* state, cudaStream_t stream) {
     const size_t amp = amp_size(ctx->dtype);
-    const size_t smem = plan->dim * plan->cols * amp;
+    const size_t smem = 2 * ROWLEVEL_STAGE_OPS * sizeof(RowOp) + plan->dim * plan->cols * amp;
     const unsigned grid = (unsigned)(plan->batch / plan->cols);
     int cl = 0;
     while ((1 << cl) < plan->cols) ++cl;
