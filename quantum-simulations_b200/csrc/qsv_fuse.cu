@@ -74,6 +74,8 @@ struct Builder {
     uint64_t relabelled_gates = 0;
     // Register bits per stage of the launch being emitted: RB (4) for the cp.async images, RB8 (3) when flush() tries the
     // radix-8 TMA image first.  Arrays stay sized for RB; with rb = 3 register bit 3 simply never occurs.
+    static constexpr int RETRY_RB4 = -1000;  // internal: the radix-8 attempt of flush() cannot hold this launch
+    int n_targets_cur = 0;                   // butterfly targets of the sweep being flushed
     int rb = RB;
     bool tma_swizzle = false;          // tile slots follow the TMA engine's 128-byte swizzle instead of swz()
     bool allow8 = true;                // (sweep_plan_build_host: complex128, QSV_NO_FFT8 unset)
@@ -470,6 +472,9 @@ struct Builder {
 
     // make room in the current launch; if it is full, close it and reopen the same stage in a new one
     int ensure_budget(Emit& e, const StageCtx& sc, size_t ops_needed, size_t slots_needed, size_t tab_needed) {
+        if (rb == RB8 && (e.ops.size() + ops_needed > MAX_OPS8 || e.gslots.size() + slots_needed > MAX_GSLOT8 ||
+                          e.tab.size() / 2 + tab_needed > MAX_TAB))
+            return RETRY_RB4;  // (the radix-8 image does not split a sweep: the four-bit attempt decides)
         if (e.ops.size() + ops_needed > MAX_OPS || e.gslots.size() + slots_needed > MAX_GSLOT || e.tab.size() / 2 + tab_needed > MAX_TAB) {
             int rc = push_sweep(e, false, nullptr);
             if (rc) return rc;
@@ -817,8 +822,6 @@ struct Builder {
         return true;
     }
 
-    static constexpr int RETRY_RB4 = -1000;  // internal: the radix-8 attempt of flush() cannot hold this launch
-
     int push_sweep(Emit& e, bool out_of_place, const std::vector<int>* out_pos_of_phys) {
         const bool has_work = std::any_of(e.ops.begin(), e.ops.end(), [](const SwOp& o) { return o.type != OP_STAGE; });
         if (!has_work && !out_of_place) {
@@ -835,7 +838,12 @@ struct Builder {
         if (rb == RB8) {
             // the radix-8 image runs FFT-shaped launches only, a handful of stages and scalars, on tiles the TMA engine can
             // move; nothing has been committed to the plan yet, so flush() can start over with four register bits
-            if (!all_fft || e.ops.size() > MAX_OPS8 || e.gslots.size() > MAX_GSLOT8 || !build_sweep8(e, out_pos_of_phys, extra8)) return RETRY_RB4;
+            // (launches that are not FFT-shaped run its generic stage loop, in place only)
+            static const bool no_gen8 = getenv("QSV_NO_GEN8") != nullptr;  // A/B aid
+            if (!has_work || (!all_fft && (out_of_place || no_gen8)) || (all_fft && n_targets_cur > 6) || e.ops.size() > MAX_OPS8 ||
+                e.gslots.size() > MAX_GSLOT8 ||
+                e.tab.size() / 2 > MAX_TAB || !build_sweep8(e, all_fft ? out_pos_of_phys : nullptr, extra8))
+                return RETRY_RB4;
         }
         SweepParams* sp = new SweepParams();
         memset(sp, 0, sizeof(*sp));
@@ -963,7 +971,7 @@ struct Builder {
         s.fused = true;
         s.params = sp;
         s.out_of_place = out_of_place;
-        s.img = all_fft ? (rb == RB8 ? IMG_FFT8 : IMG_FFT) : all_lean ? IMG_LEAN : IMG_FULL;
+        s.img = rb == RB8 ? IMG_FFT8 : all_fft ? IMG_FFT : all_lean ? IMG_LEAN : IMG_FULL;
         s.n_gates = e.n_gates;
         if (s.img == IMG_FFT8) s.tma = new Sweep8Extra(extra8);
         plan->steps.push_back(s);
@@ -986,7 +994,11 @@ struct Builder {
             n_t = __builtin_popcountll(seen);
         }
         // (a sweep whose store carries an exchange fans out over several peers: the cp.async images do that, the TMA store does not)
-        const bool try8 = allow8 && !(last_flush && carry_exchange) && k < n && k >= 9 && k <= 11 && n_t >= 1 && n_t <= 6 && n_t != 4;
+        // (FFT-shaped launches: up to six targets = two stages; generic ones may take a third stage, see push_sweep)
+        static const int gen8_max = getenv("QSV_GEN8_MAX_TARGETS") ? atoi(getenv("QSV_GEN8_MAX_TARGETS")) : 6;
+        n_targets_cur = n_t;
+        const bool try8 = allow8 && !(last_flush && carry_exchange) && k < n && k >= 9 && k <= 11 && n_t >= 1 && n_t <= std::max(6, gen8_max) &&
+                          n_t != 4;
         if (try8) {
             const size_t steps0 = plan->steps.size(), aux0 = plan->aux.size();
             const uint64_t targets0 = cur_targets;
@@ -1057,6 +1069,7 @@ struct Builder {
             finish_stage_regs(sc, want);
             // budgets: a launch carries at most MAX_OPS ops, MAX_GSLOT per-tile scalars and MAX_TAB table entries;
             // ensure_budget() closes the launch and reopens the same stage in the next one when any would overflow
+            if (rb == RB8 && e.ops.size() + 16 > MAX_OPS8) return RETRY_RB4;
             if (e.ops.size() + 16 > MAX_OPS) {
                 int rc = push_sweep(e, false, nullptr);
                 if (rc) return rc;
@@ -1217,7 +1230,9 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
         static const char* names[] = {"full", "lean", "fft16", "fft8-tma"};
         for (auto& st : best->steps)
             if (st.fused)
-                fprintf(stderr, "[qsv] sweep: image %s, %d ops, %d scalars, %llu gates%s%s\n", names[st.img], st.params->d.n_ops, st.params->d.n_gslots,
+                fprintf(stderr, "[qsv] sweep: image %s%s, %d ops, %d scalars, %llu gates%s%s\n", names[st.img],
+                        st.img == IMG_FFT8 && st.params->d.n_ops && st.params->ops[0].type == DC_STAGE ? " (generic stages)" : "", st.params->d.n_ops,
+                        st.params->d.n_gslots,
                         (unsigned long long)st.n_gates, st.out_of_place ? ", permuting store" : "",
                         st.img == IMG_FFT8 ? (st.tma->permuting ? ", tile re-ordered for the TMA store" : ", TMA store")
                                            : (st.params->d.direct_store ? ", direct store" : ""));

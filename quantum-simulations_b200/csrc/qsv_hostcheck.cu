@@ -95,7 +95,31 @@ static int sweep8_emulate_host(qsv_ctx* ctx, const SweepParams& P, const Sweep8E
                 fstage8_put<C>(tile, swz128(seg_apply(bl1, X.loc_perm)), X.boff_out[0], X.boff_out[1], X.boff_out[2], w);
             }
         }
-        for (int i = 0; i < D.n_ops && !X.mid_layout; ++i) {
+        const bool generic = D.n_ops > 0 && P.ops[0].type == DC_STAGE;
+        for (int i = 0; generic && i < D.n_ops;) {
+            // a launch that is not FFT-shaped: DC_STAGE, then the ops it holds in registers (threads in sequence: in place)
+            const OpView sop{&P.ops[i]};
+            if (sop.type() != DC_STAGE) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: op %d of a generic radix-8 launch should open a stage", i);
+            int j = i + 1;
+            while (j < D.n_ops && P.ops[j].type != DC_STAGE) ++j;
+            for (uint32_t tid = 0; tid < threads; ++tid) {
+                const uint32_t bl = expand_rb8(tid, sop.st_rpos(0), sop.st_rpos(1), sop.st_rpos(2));
+                const uint32_t a0 = swz128(bl), b0 = sop.st_roffsw(1), b1 = sop.st_roffsw(2), b2 = sop.st_roffsw(4);
+                uint32_t a[NREG8];
+                slots8(a, a0, b0, b1, b2);
+                C w[NREG8];
+                for (int r = 0; r < NREG8; ++r) w[r] = tile[a[r]];
+                for (int q = i + 1; q < j; ++q) {
+                    const OpView op{&P.ops[q]};
+                    if (op.type() >= DC_FSTAGE && op.type() < DC_FIRST_FULL) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: OP_FSTAGE in a generic launch");
+                    if (op.gmask() && (t & op.gmask()) != op.gval()) continue;
+                    generic_op8<C, R>(w, op, op.type(), (bl & op.lmask()) == op.lval(), smT.data(), smE.data(), tid);
+                }
+                fstage8_put<C>(tile, a0, b0, b1, b2, w);
+            }
+            i = j;
+        }
+        for (int i = 0; i < D.n_ops && !X.mid_layout && !generic; ++i) {
             const OpView op{&P.ops[i]};
             if (op.type() < DC_FSTAGE || op.type() >= DC_FSTAGE + 8) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: op %d of a radix-8 launch is not a radix-8 OP_FSTAGE", i);
             const bool reorder = i == D.n_ops - 1 && X.permuting;

@@ -46,6 +46,7 @@ struct Sweep8Params {
     int permuting;            // the last stage re-orders the tile for a bit-permuting store
     SegMap loc_perm;          // input-local index -> output-local index (bit permutation)
     uint16_t boff_out[RB8];   // output-order slot offset of the last stage's register bit q
+    int generic;              // the launch is not FFT-shaped: stages are DC_STAGE ops followed by generic ops
     int l2_prefetch;          // tiles ahead of the load proper that are prefetched into L2 (0 = off)
     int mid_layout;           // two-stage permuting launch through the intermediate swz() layout (Sweep8Extra)
     SegMap tmap_last;
@@ -174,7 +175,7 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
         const OpView o{&P.ops[i]};
         return expand_rb8(tid, o.rpos(0), o.rpos(1), o.rpos(2));
     };
-    for (int i = 0; i < n_ops && i < PARK8_OPS; ++i) park[i * blockDim.x + tid] = swz128(slot0(i));
+    for (int i = 0; i < n_ops && i < PARK8_OPS && !P.generic; ++i) park[i * blockDim.x + tid] = swz128(slot0(i));
     if (P.mid_layout) {  // (two stages) first stage writes swz(), last stage reads swz() with its lanes on the output order's low bits
         const uint32_t bl1 = seg_apply(tid, P.tmap_last);
         park[3 * blockDim.x + tid] = swz(slot0(0));
@@ -271,6 +272,30 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
             fstage8_compute<C, R>(op1, tile, smT, smE, pk >> 16, pk & 0xFFFFu, P.boff_last_r[0], P.boff_last_r[1], P.boff_last_r[2], w);
             __syncthreads();
             fstage8_put<C>(tile, park[2 * blockDim.x + tid], P.boff_out[0], P.boff_out[1], P.boff_out[2], w);
+        } else if (P.generic) {
+            // launches that are not FFT-shaped: a stage is a DC_STAGE op followed by the ops it holds in registers
+            for (int i = 0; i < n_ops;) {
+                const OpView sop{&P.ops[i]};
+                const uint32_t bl = expand_rb8(tid, sop.st_rpos(0), sop.st_rpos(1), sop.st_rpos(2));
+                const uint32_t a0 = swz128(bl), b0 = sop.st_roffsw(1), b1 = sop.st_roffsw(2), b2 = sop.st_roffsw(4);
+                C w[NREG8];
+                {
+                    uint32_t a[NREG8];
+                    slots8(a, a0, b0, b1, b2);
+#pragma unroll
+                    for (int j = 0; j < NREG8; ++j) w[j] = tile[a[j]];
+                }
+                for (++i; i < n_ops; ++i) {
+                    const OpView op{&P.ops[i]};
+                    const uint32_t type = op.type();
+                    if (type == DC_STAGE) break;
+                    const uint64_t gm = op.gmask();
+                    if (gm && ((uint64_t)t & gm) != op.gval()) continue;  // control on a tile-id bit not satisfied for this tile
+                    generic_op8<C, R>(w, op, type, (bl & op.lmask()) == op.lval(), smT, smE, tid);
+                }
+                fstage8_put<C>(tile, a0, b0, b1, b2, w);
+                if (i < n_ops) __syncthreads();
+            }
         } else {
             for (int i = 0; i < n_ops; ++i) {
                 const OpView op{&P.ops[i]};
@@ -363,6 +388,7 @@ int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const 
     P->loc_perm = X.loc_perm;
     static const int l2pf = getenv("QSV_L2_PREFETCH") ? atoi(getenv("QSV_L2_PREFETCH")) : 0;  // A/B aid: measured slower, see profiles/r2_ab_sweep8.txt
     P->l2_prefetch = l2pf;
+    P->generic = P->d.n_ops > 0 && P->ops[0].type == DC_STAGE;
     P->mid_layout = X.mid_layout;
     P->tmap_last = X.tmap_last;
     for (int q = 0; q < RB8; ++q) {

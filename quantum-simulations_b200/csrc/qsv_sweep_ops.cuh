@@ -20,7 +20,7 @@
 // Radix-8 image (IMG_FFT8, qsv_sweep8.cu): 3 register bits per stage, 8 amplitudes per thread, tiles moved by TMA
 #define RB8 3
 #define NREG8 8
-#define MAX_OPS8 8       // stages per launch (an FFT-shaped launch is one op per stage)
+#define MAX_OPS8 300     // ops per launch of the radix-8 image (kernel parameter space; an FFT-shaped launch is one op per stage)
 #define MAX_GSLOT8 16    // per-tile phase scalars per launch of the radix-8 image
 #define PARK8_OPS 2      // stages whose per-thread slot constants are parked in shared memory (later ones recompute them)
 #define PARK8_WORDS 4    // + the write-side constants of a permuting launch: [2] last stage (output order), [3] first stage (mid layout)
@@ -539,6 +539,16 @@ struct OpView {
     __host__ __device__ __forceinline__ uint32_t tw_abit(int s_) const { return u8_at(8 + 4 * (RB + 1) + s_); }
     __host__ __device__ __forceinline__ uint32_t rpos(int q) const { return u8_at(42 + q); }
     __host__ __device__ __forceinline__ uint32_t boff(int q) const { return u16_at(46 + 2 * q); }
+    // header of a generic op (SwOp bytes 0..23) and the payload of a stage op (roffsw[16] u16, rpos[4] u8)
+    __host__ __device__ __forceinline__ uint32_t tgt() const { return o->tgt; }
+    __host__ __device__ __forceinline__ uint32_t rmask() const { return o->rmask; }
+    __host__ __device__ __forceinline__ uint32_t rval() const { return o->rval; }
+    __host__ __device__ __forceinline__ uint32_t lmask() const { return o->lmask; }
+    __host__ __device__ __forceinline__ uint32_t lval() const { return o->lval; }
+    __host__ __device__ __forceinline__ uint64_t gmask() const { return o->gmask; }
+    __host__ __device__ __forceinline__ uint64_t gval() const { return o->gval; }
+    __host__ __device__ __forceinline__ uint32_t st_roffsw(int j) const { return u16_at(2 * j); }
+    __host__ __device__ __forceinline__ uint32_t st_rpos(int q) const { return u8_at(32 + q); }
 };
 
 template <typename C, int B, typename OP>
@@ -656,6 +666,137 @@ __host__ __device__ __forceinline__ void fstage8_put(C* tile, const uint32_t a0,
     slots8(a, a0, b0, b1, b2);
 #pragma unroll
     for (int j = 0; j < NREG8; ++j) tile[a[j]] = w[j];
+}
+
+// ---- generic ops on 8 registers (radix-8 image, launches that are not FFT-shaped) ------------------------------------
+// The same op set as generic_op below, with three register bits and every field read where it lies (OpView).
+template <typename C, typename R, bool CTRL, bool REAL, int A, typename OP>
+__host__ __device__ __forceinline__ void dense8(C (&v)[NREG8], const OP& op, const bool tpred) {
+    const uint32_t rm = op.rmask(), rv = op.rval();
+    if constexpr (REAL) {
+        const R m00 = (R)op.m(0), m01 = (R)op.m(2), m10 = (R)op.m(4), m11 = (R)op.m(6);
+#pragma unroll
+        for (int j0 = 0; j0 < NREG8; ++j0)
+            if (!(j0 & (1 << A))) {
+                const int j1 = j0 | (1 << A);
+                const C a0 = v[j0], a1 = v[j1];
+                v[j0].x = fma(m01, a1.x, m00 * a0.x);
+                v[j0].y = fma(m01, a1.y, m00 * a0.y);
+                v[j1].x = fma(m11, a1.x, m10 * a0.x);
+                v[j1].y = fma(m11, a1.y, m10 * a0.y);
+            }
+    } else {
+        const C m00 = cmake<C, R>((R)op.m(0), (R)op.m(1)), m01 = cmake<C, R>((R)op.m(2), (R)op.m(3));
+        const C m10 = cmake<C, R>((R)op.m(4), (R)op.m(5)), m11 = cmake<C, R>((R)op.m(6), (R)op.m(7));
+#pragma unroll
+        for (int j0 = 0; j0 < NREG8; ++j0)
+            if (!(j0 & (1 << A))) {
+                const int j1 = j0 | (1 << A);
+                if (!CTRL || (((j0 & rm) == rv) && tpred)) {
+                    const C a0 = v[j0], a1 = v[j1];
+                    v[j0] = cfma(m01, a1, cmul(m00, a0));
+                    v[j1] = cfma(m11, a1, cmul(m10, a0));
+                }
+            }
+    }
+}
+template <typename C, int A, typename OP>
+__host__ __device__ __forceinline__ void permx8(C (&v)[NREG8], const OP& op, const bool tpred) {
+    const uint32_t rm = op.rmask(), rv = op.rval();
+#pragma unroll
+    for (int j0 = 0; j0 < NREG8; ++j0)
+        if (!(j0 & (1 << A))) {
+            const int j1 = j0 | (1 << A);
+            if (((j0 & rm) == rv) && tpred) {
+                const C t = v[j0];
+                v[j0] = v[j1];
+                v[j1] = t;
+            }
+        }
+}
+template <typename C, typename R, typename OP>
+__host__ __device__ __forceinline__ void wtable8(C (&v)[NREG8], const OP& op, const double2* __restrict__ smT) {
+    const double2* w = smT + op.u16_at(0);
+    const uint32_t wm = op.u16_at(2);
+#pragma unroll
+    for (int j = 0; j < NREG8; ++j)
+        if ((wm >> j) & 1) {
+            const double2 ww = w[j];
+            v[j] = cmul(v[j], cmake<C, R>((R)ww.x, (R)ww.y));
+        }
+}
+template <typename C, typename R, typename OP>
+__host__ __device__ __forceinline__ void twid8_math(C (&v)[NREG8], const OP& op, const double2* __restrict__ smT, const double2* __restrict__ smE,
+                                                    const uint32_t tid) {
+    const uint32_t c_lo = tid & 15u, c_hi = 16u + (tid >> 4);
+    const double scale = op.m(0);
+    const uint32_t ts0 = op.tw_tslot(RB), gs0 = op.tw_gslot(RB);
+    if (ts0 != NONE16 || gs0 != NONE16) {
+        double2 c0 = make_double2(scale, 0.0);
+        if (gs0 != NONE16) {
+            const double2 g0 = smE[gs0];
+            c0 = make_double2(scale * g0.x, scale * g0.y);
+        }
+        if (ts0 != NONE16) c0 = cmul(c0, cmul(smT[ts0 + c_lo], smT[ts0 + c_hi]));
+        const C cc = cmake<C, R>((R)c0.x, (R)c0.y);
+#pragma unroll
+        for (int j = 0; j < NREG8; ++j) v[j] = cmul(v[j], cc);
+    } else if (scale != 1.0) {
+        const R sc = (R)scale;
+#pragma unroll
+        for (int j = 0; j < NREG8; ++j) {
+            v[j].x *= sc;
+            v[j].y *= sc;
+        }
+    }
+#define TWID8_BIT(B)                                                            \
+    if (op.tw_abit(B) != 0xFFu) {                                               \
+        double2 e = make_double2(1.0, 0.0);                                     \
+        const uint32_t gsl = op.tw_gslot(B), tsl = op.tw_tslot(B);              \
+        if (gsl != NONE16) e = smE[gsl];                                        \
+        if (tsl != NONE16) e = cmul(e, cmul(smT[tsl + c_lo], smT[tsl + c_hi])); \
+        mul_bit_n<C, NREG8, B>(v, e);                                           \
+    }
+    TWID8_BIT(0)
+    TWID8_BIT(1)
+    TWID8_BIT(2)
+#undef TWID8_BIT
+}
+
+template <typename C, typename R, typename OP>
+__host__ __device__ __forceinline__ void generic_op8(C (&v)[NREG8], const OP& op, const uint32_t type, const bool tpred,
+                                                     const double2* __restrict__ smT, const double2* __restrict__ smE, const uint32_t tid) {
+    switch (type) {
+        case DC_DENSE_REAL_NC + 0: dense8<C, R, false, true, 0>(v, op, tpred); break;
+        case DC_DENSE_REAL_NC + 1: dense8<C, R, false, true, 1>(v, op, tpred); break;
+        case DC_DENSE_REAL_NC + 2: dense8<C, R, false, true, 2>(v, op, tpred); break;
+        case DC_DENSE_CPLX_NC + 0: dense8<C, R, false, false, 0>(v, op, tpred); break;
+        case DC_DENSE_CPLX_NC + 1: dense8<C, R, false, false, 1>(v, op, tpred); break;
+        case DC_DENSE_CPLX_NC + 2: dense8<C, R, false, false, 2>(v, op, tpred); break;
+        case DC_DENSE_CPLX_C + 0: dense8<C, R, true, false, 0>(v, op, tpred); break;
+        case DC_DENSE_CPLX_C + 1: dense8<C, R, true, false, 1>(v, op, tpred); break;
+        case DC_DENSE_CPLX_C + 2: dense8<C, R, true, false, 2>(v, op, tpred); break;
+        case DC_PERMX + 0: permx8<C, 0>(v, op, tpred); break;
+        case DC_PERMX + 1: permx8<C, 1>(v, op, tpred); break;
+        case DC_PERMX + 2: permx8<C, 2>(v, op, tpred); break;
+        case DC_MPHASE: {
+            const C d = cmake<C, R>((R)op.m(0), (R)op.m(1));
+            const uint32_t rm = op.rmask(), rv = op.rval();
+#pragma unroll
+            for (int j = 0; j < NREG8; ++j)
+                if (((j & rm) == rv) && tpred) v[j] = cmul(v[j], d);
+            break;
+        }
+        case DC_HADD + 0: hadd_n<C, NREG8, 0>(v); break;
+        case DC_HADD + 1: hadd_n<C, NREG8, 1>(v); break;
+        case DC_HADD + 2: hadd_n<C, NREG8, 2>(v); break;
+        case DC_W: wtable8<C, R>(v, op, smT); break;
+        case DC_HW + 0: hadd_n<C, NREG8, 0>(v); wtable8<C, R>(v, op, smT); break;
+        case DC_HW + 1: hadd_n<C, NREG8, 1>(v); wtable8<C, R>(v, op, smT); break;
+        case DC_HW + 2: hadd_n<C, NREG8, 2>(v); wtable8<C, R>(v, op, smT); break;
+        case DC_TWID: twid8_math<C, R>(v, op, smT, smE, tid); break;
+        default: break;
+    }
 }
 
 // One op of the generic interpreter applied to a thread's 16 registers (everything but the stage changes).
