@@ -995,7 +995,12 @@ struct Builder {
         }
         // (a sweep whose store carries an exchange fans out over several peers: the cp.async images do that, the TMA store does not)
         // (FFT-shaped launches: up to six targets = two stages; generic ones may take a third stage, see push_sweep)
-        static const int gen8_max = getenv("QSV_GEN8_MAX_TARGETS") ? atoi(getenv("QSV_GEN8_MAX_TARGETS")) : 6;
+        // A sweep of swaps and phases only (multi-controlled X streams) is cheap per stage: measured faster in three radix-8
+        // stages than in two or three radix-16 ones (cyclic shift, 2^30: 25.2 against 28.7 ms), so it may carry up to 9 targets.
+        bool dense = false;
+        for (size_t gi : cur) dense |= pg[gi].kind == QSV_DENSE1;
+        static const int gen8_env = getenv("QSV_GEN8_MAX_TARGETS") ? atoi(getenv("QSV_GEN8_MAX_TARGETS")) : 0;
+        const int gen8_max = gen8_env ? gen8_env : (dense ? 6 : 9);
         n_targets_cur = n_t;
         const bool try8 = allow8 && !(last_flush && carry_exchange) && k < n && k >= 9 && k <= 11 && n_t >= 1 && n_t <= std::max(6, gen8_max) &&
                           n_t != 4;
@@ -1224,6 +1229,26 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
             }
             delete best;
             best = p;
+        }
+        // Tried and measured worse (profiles/r2_ab_generic8.txt), kept behind QSV_COST_MODEL=1: trading launches for cheaper
+        // ones.  A sweep of at most six targets is eligible for the radix-8 / TMA image; for 96 random controlled dense gates
+        // the six-target plan has 14 sweeps of 5.8-7.8 ms instead of 11 of 7.0-9.1 ms -- 95.4 against 86.2 ms per step.
+        auto cost = [](const SweepPlan* p) {
+            double c = 0;
+            for (auto& st : p->steps) c += !st.fused ? 1.0 : st.img == IMG_FFT8 ? 1.0 : st.img == IMG_FFT ? 1.1 : 1.4;
+            return c;
+        };
+        static const bool use_cost = getenv("QSV_COST_MODEL") != nullptr;  // A/B aid
+        if (use_cost && ctx->dtype == QSV_C128 && k >= 9 && k <= 11) {
+            SweepPlan* p = nullptr;
+            if (build(6, &p) == QSV_OK) {
+                if (cost(p) < cost(best)) {
+                    delete best;
+                    best = p;
+                } else {
+                    delete p;
+                }
+            }
         }
     }
     if (getenv("QSV_PLAN_DEBUG")) {
