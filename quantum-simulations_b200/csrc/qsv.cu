@@ -37,7 +37,7 @@ enum { MODE_DENSE = 0, MODE_SWAP = 1, MODE_DIAG = 2 };
 
 template <typename R, int MODE, int U>
 __global__ void __launch_bounds__(256) k_gate1(typename cplx_of<R>::type* __restrict__ st, uint64_t npairs,
-                                               BitInsert ins, uint64_t tmask, Mat2 mat) {
+                                               const __grid_constant__ BitInsert ins, uint64_t tmask, Mat2 mat) {
     typedef typename cplx_of<R>::type C;
     const uint64_t base = (uint64_t)blockIdx.x * (256 * U) + threadIdx.x;
     uint64_t i0[U];
@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(256) k_gate1_shfl(typename cplx_of<R>::type* _
 // K3 special case diag(1, d): only amplitudes with the target bit set are touched
 template <typename R, int U>
 __global__ void __launch_bounds__(256) k_phase1(typename cplx_of<R>::type* __restrict__ st, uint64_t namps,
-                                                BitInsert ins, double dre, double dim) {
+                                                const __grid_constant__ BitInsert ins, double dre, double dim) {
     typedef typename cplx_of<R>::type C;
     const uint64_t base = (uint64_t)blockIdx.x * (256 * U) + threadIdx.x;
     const C d = cmake<C, R>((R)dre, (R)dim);
@@ -139,7 +139,7 @@ struct TargetSet { int t; uint64_t mask[QSV_MAX_TARGETS]; };  // mask[j] = bit o
 
 template <typename R, int T>
 __global__ void __launch_bounds__(128) k_densek(typename cplx_of<R>::type* __restrict__ st, uint64_t ngroups,
-                                                BitInsert ins, TargetSet ts, const double* __restrict__ mat) {
+                                                const __grid_constant__ BitInsert ins, TargetSet ts, const double* __restrict__ mat) {
     typedef typename cplx_of<R>::type C;
     constexpr int D = 1 << T;
     __shared__ double2 sm[D * D];
@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(256) k_rows2(typename cplx_of<R>::type* __rest
 // ================================================================================================
 template <typename R>
 __global__ void k_basis(typename cplx_of<R>::type* __restrict__ st, uint64_t ncols, int batch_bits, uint64_t col0,
-                        BitInsert anc) {
+                        const __grid_constant__ BitInsert anc) {
     typedef typename cplx_of<R>::type C;
     const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= ncols) return;
@@ -240,7 +240,7 @@ __global__ void k_basis(typename cplx_of<R>::type* __restrict__ st, uint64_t nco
 template <typename R>
 __global__ void __launch_bounds__(256) k_project(const typename cplx_of<R>::type* __restrict__ in,
                                                  typename cplx_of<R>::type* __restrict__ out, uint64_t nout,
-                                                 BitInsert anc) {
+                                                 const __grid_constant__ BitInsert anc) {
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nout; i += stride)
         out[i] = in[bit_expand(i, anc)];
@@ -251,7 +251,7 @@ struct Psi { double a_re, a_im, b_re, b_im; };
 
 template <typename R>
 __global__ void k_basis_psi(typename cplx_of<R>::type* __restrict__ st, uint64_t ncols, int batch_bits, uint64_t col0,
-                            BitInsert anc, Psi psi) {
+                            const __grid_constant__ BitInsert anc, Psi psi) {
     typedef typename cplx_of<R>::type C;
     const uint64_t id = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t j = id % ncols, v = id / ncols;
@@ -270,7 +270,7 @@ __global__ void k_basis_psi(typename cplx_of<R>::type* __restrict__ st, uint64_t
 template <typename R>
 __global__ void __launch_bounds__(256) k_project_psi(const typename cplx_of<R>::type* __restrict__ in,
                                                      typename cplx_of<R>::type* __restrict__ out, uint64_t nout,
-                                                     BitInsert anc, Psi psi) {
+                                                     const __grid_constant__ BitInsert anc, Psi psi) {
     typedef typename cplx_of<R>::type C;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nout; i += stride) {
@@ -296,7 +296,7 @@ struct BitPerm { int n; uint8_t to[64]; };
 template <typename R>
 __global__ void __launch_bounds__(256) k_permute_bits(const typename cplx_of<R>::type* __restrict__ in,
                                                       typename cplx_of<R>::type* __restrict__ out, uint64_t n,
-                                                      BitPerm bp, int fixed_low) {
+                                                      const __grid_constant__ BitPerm bp, int fixed_low) {
     // threads walk the OUTPUT index so that stores coalesce; bits below fixed_low map to themselves
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t y = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; y < n; y += stride) {
