@@ -23,6 +23,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--n", type=int, default=10)
     ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--as-rank", default="", help="R/W: on ONE GPU, do what rank R of W would do (its block of columns only)")
     args = ap.parse_args()
     import torch
     from quantum_simulations_b200.engine import Engine
@@ -32,11 +33,18 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
+    solo = None
+    if args.as_rank:
+        assert world == 1
+        r_, w_ = (int(x) for x in args.as_rank.split("/"))
+        solo = (r_, w_)
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     n = args.n
     N = 1 << n
+    if solo:
+        rank, world = solo
     assert N % world == 0
     cols = N // world
     cb = cols.bit_length() - 1
@@ -67,20 +75,20 @@ def main():
             times.append(a.elapsed_time(b))
     mx, bad = eng.compare(res, expected, rtol=1e-5, atol=1e-8)        # K8: np.allclose(v, u) on the device
     ms = float(np.median(times))
-    if world > 1:
+    if world > 1 and not solo:
         t = torch.tensor([ms, mx, float(bad)], device=f"cuda:{local_rank}", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, mx, bad = float(t[0]), float(t[1]), int(t[2])
-    if rank == 0:
+    if rank == 0 or solo:
         flops = 28.0 * len(stream) * N          # 28 real flops per 2x2 complex butterfly, per column, whole job
-        print(json.dumps({"config": f"random 2^{n} unitary, SINGLET stream, {N}-column reconstruction, complex128, {world} B200"
+        print(json.dumps({"config": f"random 2^{n} unitary, SINGLET stream, {N}-column reconstruction, complex128, {world} B200" + (f" [rank {rank} alone on one GPU]" if solo else "")
                                     + (f" ({cols} columns each, no collective)" if world > 1 else ""),
                           "gates": int(len(recs)), "two_level_ops": len(stream), "fused_passes": sweeps, "n_gpus": world, "ms": ms,
                           "gates_per_sec": len(recs) / (ms / 1e3), "fp64_GFLOPs": flops / (ms / 1e3) / 1e9,
                           "max_abs_err_vs_input": mx, "allclose_violations": bad,
                           "host_s": {"two_level_stream": round(t1 - t0, 1), "singlet_records": round(t2 - t1, 1),
                                      "plan (fold relabels, level schedule, upload)": round(t4 - t3, 2)}}))
-    if world > 1:
+    if world > 1 and not solo:
         dist.destroy_process_group()
 
 
