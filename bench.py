@@ -404,6 +404,18 @@ def run_single(args):
         avg_ms = ms / max(1, launches)
         achieved = st["amp_bytes"] / sec / 1e9
     amp_gbps = st["amp_bytes"] / sec / 1e9
+    # arithmetic of the circuit itself: 28 real flops per 2x2 complex butterfly on the amplitude pairs a gate touches
+    # (SURVEY.md 8d); diagonal gates 6 per touched amplitude.  Dense-gate streams are bound by this, not by HBM.
+    flop = 0.0
+    for r in recs:
+        c = bin(int(r["ctrl_mask"])).count("1")
+        kind = int(r["kind"])
+        if kind == 0:
+            flop += 28.0 * (amps >> (c + 1))
+        elif kind == 2:
+            flop += 6.0 * (amps >> c)
+    compute = {"fp64_flop_per_step": flop, "achieved_TFLOPs": flop * args.steps / sec / 1e12,
+               "note": "algorithmic FP64 work of the gate stream / step time; B200's FP64 vector rate is nominally ~37-40 TFLOP/s (not measured on this pool)"}
     # ---- e2e through host buffers -------------------------------------------------------------
     # Every step uploads its input state from pinned host memory, applies the circuit and downloads the result.
     # Steps are independent jobs, so they are pipelined over three device buffers and three streams: the download of
@@ -489,6 +501,7 @@ def run_single(args):
             "roofline": {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": achieved / peak, "frac_of_nominal_8TBps": achieved / 8000.0, "bytes_per_launch": per_launch_bytes,
                          "avg_launch_ms": avg_ms, "traffic": traffic, "traffic_source": traffic_src},
+            "compute": compute,
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "sweep_ms_first_step": sweep_ms,
             "check": check, "max_abs_err": check.get("max_abs_err") if check else None}
     print(json.dumps(line))
