@@ -414,8 +414,10 @@ def run_single(args):
             flop += 28.0 * (amps >> (c + 1))
         elif kind == 2:
             flop += 6.0 * (amps >> c)
-    compute = {"fp64_flop_per_step": flop, "achieved_TFLOPs": flop * args.steps / sec / 1e12,
-               "note": "algorithmic FP64 work of the gate stream / step time; B200's FP64 vector rate is nominally ~37-40 TFLOP/s (not measured on this pool)"}
+    compute = None
+    if workload_kind() == "random":   # (diagonal runs of QFT-like streams are merged by the fusion pass: their gate-by-gate count says nothing)
+        compute = {"fp64_flop_per_step": flop, "achieved_TFLOPs": flop * args.steps / sec / 1e12,
+                   "note": "algorithmic FP64 work of the gate stream / step time; B200's FP64 vector rate is nominally ~37-40 TFLOP/s (not measured on this pool)"}
     # ---- e2e through host buffers -------------------------------------------------------------
     # Every step uploads its input state from pinned host memory, applies the circuit and downloads the result.
     # Steps are independent jobs, so they are pipelined over three device buffers and three streams: the download of

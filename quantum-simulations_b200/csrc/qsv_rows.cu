@@ -48,19 +48,27 @@ struct RowSlabPlan {
 // with cp.async while level l computes (two buffers), so that no pass of a level waits on L2 and no op sits in registers.
 #define ROWLEVEL_STAGE_OPS 512   // ops per staging buffer (40 KB); wider levels (never seen for Givens streams) read the rest from L2
 
-template <typename R>
-__global__ void __launch_bounds__(1024, 1) k_rowlevels(typename cplx_of<R>::type* __restrict__ st, uint64_t dim, uint64_t batch, int cols_log2,
-                                                      const RowOp* __restrict__ ops, const uint32_t* __restrict__ level_start,
-                                                      uint32_t n_levels) {
+// One THREAD per op, all COLS columns of the CTA's slab in its registers: the 80-byte op record is then read once per op
+// instead of once per (op, column) -- ncu of the (op, column)-per-thread version showed the shared-memory pipe 80 % busy,
+// more than half of it on op records (profiles/r2q_ncu_full_rowlevels_config4.csv) -- and the 2 x COLS butterflies of a
+// thread are independent.  Rows are stored with the column index XOR-ed with the row number, so that lanes holding
+// different rows read different banks.
+template <typename R, int COLS>
+__global__ void __launch_bounds__(512, 1) k_rowlevels(typename cplx_of<R>::type* __restrict__ st, uint64_t dim, uint64_t batch,
+                                                     const RowOp* __restrict__ ops, const uint32_t* __restrict__ level_start,
+                                                     uint32_t n_levels) {
     typedef typename cplx_of<R>::type C;
+    constexpr int CL = COLS == 1 ? 0 : COLS == 2 ? 1 : COLS == 4 ? 2 : 3;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RowOp* stage = reinterpret_cast<RowOp*>(smem_raw);                                        // [2][ROWLEVEL_STAGE_OPS]
-    C* slab = reinterpret_cast<C*>(smem_raw + 2 * ROWLEVEL_STAGE_OPS * sizeof(RowOp));        // [dim][cols]
+    C* slab = reinterpret_cast<C*>(smem_raw + 2 * ROWLEVEL_STAGE_OPS * sizeof(RowOp));        // [dim][COLS], column c of row r at c ^ (r % COLS)
     const uint32_t tid = threadIdx.x, T = blockDim.x;
-    const uint32_t cols = 1u << cols_log2, cmask = cols - 1u;
-    const uint64_t col0 = (uint64_t)blockIdx.x << cols_log2;
-    const uint64_t slab_amps = dim << cols_log2;
-    for (uint64_t i = tid; i < slab_amps; i += T) slab[i] = st[(i >> cols_log2) * batch + col0 + (i & cmask)];
+    const uint64_t col0 = (uint64_t)blockIdx.x << CL;
+    const uint64_t slab_amps = dim << CL;
+    for (uint64_t i = tid; i < slab_amps; i += T) {
+        const uint64_t r = i >> CL, c = i & (COLS - 1);
+        slab[(r << CL) | (c ^ (r & (COLS - 1)))] = st[r * batch + col0 + c];
+    }
     auto stage_level = [&](uint32_t first, uint32_t last, int buf) {  // all threads: 16-byte pieces of the level's op records
         const uint32_t n = min(last - first, (uint32_t)ROWLEVEL_STAGE_OPS);
         const char* src = reinterpret_cast<const char*>(ops + first);
@@ -71,24 +79,34 @@ __global__ void __launch_bounds__(1024, 1) k_rowlevels(typename cplx_of<R>::type
         }
         asm volatile("cp.async.commit_group;\n" ::);
     };
-    auto apply = [&](const RowOp& o, uint32_t col) {
-        C* p0 = slab + ((uint64_t)o.r0 << cols_log2) + col;
-        C* p1 = slab + ((uint64_t)o.r1 << cols_log2) + col;
-        const C a0 = *p0, a1 = *p1;
+    auto apply = [&](const RowOp& o) {
+        C* p0 = slab + ((uint64_t)o.r0 << CL);
+        C* p1 = slab + ((uint64_t)o.r1 << CL);
+        const uint32_t x0 = o.r0 & (COLS - 1), x1 = o.r1 & (COLS - 1);
+        C a0[COLS], a1[COLS];
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) {
+            a0[c] = p0[c ^ x0];
+            a1[c] = p1[c ^ x1];
+        }
         if (o.swap) {
-            *p0 = a1;
-            *p1 = a0;
+#pragma unroll
+            for (int c = 0; c < COLS; ++c) {
+                p0[c ^ x0] = a1[c];
+                p1[c ^ x1] = a0[c];
+            }
         } else {
             const C m00 = cmake<C, R>((R)o.m[0], (R)o.m[1]), m01 = cmake<C, R>((R)o.m[2], (R)o.m[3]);
             const C m10 = cmake<C, R>((R)o.m[4], (R)o.m[5]), m11 = cmake<C, R>((R)o.m[6], (R)o.m[7]);
-            *p0 = cfma(m01, a1, cmul(m00, a0));
-            *p1 = cfma(m11, a1, cmul(m10, a0));
+#pragma unroll
+            for (int c = 0; c < COLS; ++c) {
+                p0[c ^ x0] = cfma(m01, a1[c], cmul(m00, a0[c]));
+                p1[c ^ x1] = cfma(m11, a1[c], cmul(m10, a0[c]));
+            }
         }
     };
     uint32_t s = n_levels ? level_start[0] : 0, e = n_levels ? level_start[1] : 0;
     if (n_levels) stage_level(s, e, 0);
-    const uint32_t per_pass = T >> cols_log2;  // ops one pass of the CTA covers
-    const uint32_t my_op = tid >> cols_log2, my_col = tid & cmask;
     for (uint32_t l = 0; l < n_levels; ++l) {
         const uint32_t s2 = e, e2 = level_start[l + 2];   // (two padding entries follow the last level)
         asm volatile("cp.async.wait_group 0;\n" ::: "memory");
@@ -96,12 +114,32 @@ __global__ void __launch_bounds__(1024, 1) k_rowlevels(typename cplx_of<R>::type
         if (l + 1 < n_levels) stage_level(s2, e2, (l + 1) & 1);
         const RowOp* cur = stage + (l & 1) * ROWLEVEL_STAGE_OPS;
         const uint32_t n = e - s;
-        for (uint32_t i = my_op; i < n; i += per_pass) apply(i < ROWLEVEL_STAGE_OPS ? cur[i] : ops[s + i], my_col);
+        for (uint32_t i = tid; i < n; i += T) apply(i < ROWLEVEL_STAGE_OPS ? cur[i] : ops[s + i]);
         s = s2;
         e = e2;
     }
     __syncthreads();
-    for (uint64_t i = tid; i < slab_amps; i += T) st[(i >> cols_log2) * batch + col0 + (i & cmask)] = slab[i];
+    for (uint64_t i = tid; i < slab_amps; i += T) {
+        const uint64_t r = i >> CL, c = i & (COLS - 1);
+        st[r * batch + col0 + c] = slab[(r << CL) | (c ^ (r & (COLS - 1)))];
+    }
+}
+
+template <typename R>
+static cudaError_t rowlevels_dispatch(bool attr_only, int cols, int smem, unsigned grid, int threads, cudaStream_t stream, void* st, uint64_t dim,
+                                      uint64_t batch, const RowOp* ops, const uint32_t* ls, uint32_t n_levels) {
+    typedef typename cplx_of<R>::type C;
+#define RL(COLS)                                                                                                             \
+    if (attr_only) return cudaFuncSetAttribute(k_rowlevels<R, COLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);     \
+    k_rowlevels<R, COLS><<<grid, threads, smem, stream>>>((C*)st, dim, batch, ops, ls, n_levels);                            \
+    return cudaGetLastError();
+    switch (cols) {
+        case 1: RL(1)
+        case 2: RL(2)
+        case 4: RL(4)
+        default: RL(8)
+    }
+#undef RL
 }
 
 void rowslab_free(RowSlabPlan* p) { delete p; }
@@ -120,7 +158,7 @@ int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out) {
     const size_t budget = 224 * 1024 - 2 * ROWLEVEL_STAGE_OPS * sizeof(RowOp);
     uint64_t cols = budget / (dim * amp);
     if (cols < 1) return QSV_E_UNSUPPORTED;
-    cols = std::min<uint64_t>(std::min<uint64_t>(cols, 32), batch);
+    cols = std::min<uint64_t>(std::min<uint64_t>(cols, 8), batch);   // (a thread holds 2 x cols amplitudes in registers)
     while (cols & (cols - 1)) cols &= cols - 1;  // power of two
     {
         // The work per level is fixed per COLUMN, and a level's latency (barrier + one trip through shared memory) does not
@@ -209,10 +247,10 @@ int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out) {
     plan->batch = batch;
     plan->cols = (int)cols;
     {
-        // CTA size: enough threads for the widest common level (dim/2 ops at most), a multiple of the warp, at most 1024
-        uint64_t want = std::min<uint64_t>((dim / 2) * cols, 1024);
-        want = std::max<uint64_t>(want, std::max<uint64_t>(32, cols));
-        plan->threads = (int)((want + 31) / 32 * 32);
+        // CTA size: one thread per op of the widest level, a multiple of the warp, at most 512
+        uint32_t widest = 1;
+        for (uint32_t l = 0; l < n_levels; ++l) widest = std::max(widest, start[l + 1] - start[l]);
+        plan->threads = (int)std::min<uint32_t>(512, (widest + 31) / 32 * 32);
     }
     if (!ops.empty()) {
         cudaError_t e = cudaMalloc(&plan->d_ops, sorted.size() * sizeof(RowOp));
@@ -225,8 +263,9 @@ int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out) {
         }
     }
     const int smem = (int)(2 * ROWLEVEL_STAGE_OPS * sizeof(RowOp) + dim * cols * amp);
-    cudaError_t e = ctx->dtype == QSV_C128 ? cudaFuncSetAttribute(k_rowlevels<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                                           : cudaFuncSetAttribute(k_rowlevels<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = ctx->dtype == QSV_C128
+                        ? rowlevels_dispatch<double>(true, (int)cols, smem, 0, 0, nullptr, nullptr, 0, 0, nullptr, nullptr, 0)
+                        : rowlevels_dispatch<float>(true, (int)cols, smem, 0, 0, nullptr, nullptr, 0, 0, nullptr, nullptr, 0);
     if (e != cudaSuccess) {
         delete plan;
         return qsv_fail(ctx, QSV_E_CUDA, "cudaFuncSetAttribute(%d B smem) failed: %s", smem, cudaGetErrorString(e));
@@ -237,18 +276,14 @@ int rowslab_build(qsv_ctx* ctx, RowSlabPlan** out) {
 
 int rowslab_run(qsv_ctx* ctx, RowSlabPlan* plan, void* state, cudaStream_t stream) {
     const size_t amp = amp_size(ctx->dtype);
-    const size_t smem = 2 * ROWLEVEL_STAGE_OPS * sizeof(RowOp) + plan->dim * plan->cols * amp;
+    const int smem = (int)(2 * ROWLEVEL_STAGE_OPS * sizeof(RowOp) + plan->dim * plan->cols * amp);
     const unsigned grid = (unsigned)(plan->batch / plan->cols);
-    int cl = 0;
-    while ((1 << cl) < plan->cols) ++cl;
     if (plan->n_ops) {
-        if (ctx->dtype == QSV_C128)
-            k_rowlevels<double><<<grid, plan->threads, smem, stream>>>((double2*)state, plan->dim, plan->batch, cl, plan->d_ops,
-                                                                      plan->d_level_start, (uint32_t)plan->n_levels);
-        else
-            k_rowlevels<float><<<grid, plan->threads, smem, stream>>>((float2*)state, plan->dim, plan->batch, cl, plan->d_ops,
-                                                                     plan->d_level_start, (uint32_t)plan->n_levels);
-        QSV_CUDA(ctx, cudaGetLastError());
+        QSV_CUDA(ctx, ctx->dtype == QSV_C128
+                          ? rowlevels_dispatch<double>(false, plan->cols, smem, grid, plan->threads, stream, state, plan->dim, plan->batch,
+                                                       plan->d_ops, plan->d_level_start, (uint32_t)plan->n_levels)
+                          : rowlevels_dispatch<float>(false, plan->cols, smem, grid, plan->threads, stream, state, plan->dim, plan->batch,
+                                                      plan->d_ops, plan->d_level_start, (uint32_t)plan->n_levels));
         ctx->stats.kernel_launches++;
     }
     ctx->stats.sweeps++;
