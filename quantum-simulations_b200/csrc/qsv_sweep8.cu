@@ -46,6 +46,7 @@ struct Sweep8Params {
     int permuting;            // the last stage re-orders the tile for a bit-permuting store
     SegMap loc_perm;          // input-local index -> output-local index (bit permutation)
     uint16_t boff_out[RB8];   // output-order slot offset of the last stage's register bit q
+    int l2_hint;              // A/B aid: 1 = evict_first on loads, 2 = on stores, 3 = both
     int generic;              // the launch is not FFT-shaped: stages are DC_STAGE ops followed by generic ops
     int l2_prefetch;          // tiles ahead of the load proper that are prefetched into L2 (0 = off)
     int mid_layout;           // two-stage permuting launch through the intermediate swz() layout (Sweep8Extra)
@@ -83,9 +84,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // one box: global -> shared, completion counted on the mbarrier.  (No multicast: every CTA fetches its own tile.)
-__device__ __forceinline__ void tma_load(const CUtensorMap* tm, void* smem_dst, uint64_t* bar, int rank, int c1, int c2, int c3, int c4) {
+// `policy` != 0: an L2 cache-policy word (createpolicy) rides along -- A/B aid, see sweep8_launch.
+__device__ __forceinline__ void tma_load(const CUtensorMap* tm, void* smem_dst, uint64_t* bar, int rank, int c1, int c2, int c3, int c4,
+                                         uint64_t policy = 0) {
     const uint32_t d = smem_u32(smem_dst), b = smem_u32(bar);
     const uint64_t m = reinterpret_cast<uint64_t>(tm);
+    if (policy && rank == 3) {
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(d),
+            "l"(m), "r"(b), "r"(0), "r"(c1), "r"(c2), "l"(policy)
+            : "memory");
+        return;
+    }
     switch (rank) {
         case 2:
             asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(d),
@@ -127,9 +137,15 @@ __device__ __forceinline__ void tma_prefetch_l2(const CUtensorMap* tm, int rank,
     }
 }
 // one box: shared -> global (bulk async group)
-__device__ __forceinline__ void tma_store(const CUtensorMap* tm, const void* smem_src, int rank, int c1, int c2, int c3, int c4) {
+__device__ __forceinline__ void tma_store(const CUtensorMap* tm, const void* smem_src, int rank, int c1, int c2, int c3, int c4, uint64_t policy = 0) {
     const uint32_t s = smem_u32(smem_src);
     const uint64_t m = reinterpret_cast<uint64_t>(tm);
+    if (policy && rank == 3) {
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group.L2::cache_hint [%0, {%2, %3, %4}], [%1], %5;" ::"l"(m), "r"(s), "r"(0),
+                     "r"(c1), "r"(c2), "l"(policy)
+                     : "memory");
+        return;
+    }
     switch (rank) {
         case 2:
             asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(m), "r"(s), "r"(0), "r"(c1) : "memory");
@@ -210,13 +226,16 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
         c3 = T.rank > 3 ? (int)((p >> T.shift[3]) & ((1ull << T.bits[3]) - 1ull)) : 0;
         c4 = T.rank > 4 ? (int)((p >> T.shift[4]) & ((1ull << T.bits[4]) - 1ull)) : 0;
     };
+    uint64_t pol = 0;
+    if (P.l2_hint) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    const uint64_t pol_ld = (P.l2_hint & 1) ? pol : 0, pol_st = (P.l2_hint & 2) ? pol : 0;
     auto issue_load = [&](uint32_t t, int b) {  // one thread
         const uint64_t phys = seg_apply64x(t, D.in_glob);
         mbar_expect_tx(&mbar[b], tile_bytes);
         for (int e = 0; e < P.in.n_inst; ++e) {
             int c1, c2, c3, c4;
             box_coords(P.in, phys | P.in.inst_goff[e], c1, c2, c3, c4);
-            tma_load(&tm_in, smem_raw + (size_t)b * tile_bytes + (size_t)e * P.in.inst_amps * sizeof(C), &mbar[b], P.in.rank, c1, c2, c3, c4);
+            tma_load(&tm_in, smem_raw + (size_t)b * tile_bytes + (size_t)e * P.in.inst_amps * sizeof(C), &mbar[b], P.in.rank, c1, c2, c3, c4, pol_ld);
         }
     };
     auto issue_prefetch = [&](uint32_t t) {  // one thread
@@ -232,7 +251,7 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
         for (int e = 0; e < P.out.n_inst; ++e) {
             int c1, c2, c3, c4;
             box_coords(P.out, phys | P.out.inst_goff[e], c1, c2, c3, c4);
-            tma_store(&tm_out, smem_raw + (size_t)b * tile_bytes + (size_t)e * P.out.inst_amps * sizeof(C), P.out.rank, c1, c2, c3, c4);
+            tma_store(&tm_out, smem_raw + (size_t)b * tile_bytes + (size_t)e * P.out.inst_amps * sizeof(C), P.out.rank, c1, c2, c3, c4, pol_st);
         }
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     };
@@ -388,6 +407,8 @@ int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const 
     P->loc_perm = X.loc_perm;
     static const int l2pf = getenv("QSV_L2_PREFETCH") ? atoi(getenv("QSV_L2_PREFETCH")) : 0;  // A/B aid: measured slower, see profiles/r2_ab_sweep8.txt
     P->l2_prefetch = l2pf;
+    static const int l2_hint = getenv("QSV_L2_HINT") ? atoi(getenv("QSV_L2_HINT")) : 0;  // A/B aid
+    P->l2_hint = l2_hint;
     P->generic = P->d.n_ops > 0 && P->ops[0].type == DC_STAGE;
     P->mid_layout = X.mid_layout;
     P->tmap_last = X.tmap_last;
