@@ -557,3 +557,32 @@ print("ok")
         env = dict(os.environ, **extra)
         out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
         assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+
+
+@pytest.mark.parametrize("tile_bits", [9, 11])
+def test_fused_runs_repeat_bit_for_bit(tile_bits, monkeypatch):
+    """compute-sanitizer is closed on this pool, so shared-memory hazards of the staged kernels (stage barriers, the TMA
+    engine's reads and writes of the tile buffers, the re-ordering store) are guarded the indirect way: the same plan run
+    five times on the same input must give the same BITS, for a QFT (radix-8 TMA image, permuting store through the
+    intermediate layout) and for a stream of controlled dense gates and swaps (generic stage loop / interpreter images)."""
+    from quantum_simulations_b200.program import Program
+    from quantum_simulations_b200.utils.mgen import qft_program
+    monkeypatch.setenv("QSV_TILE_BITS", str(tile_bits))
+    rng = np.random.default_rng(9)
+    n = 17
+    mixed = Program([qs.Qubit(i) for i in range(n)])
+    for i in range(120):
+        bits = rng.choice(n, size=3, replace=False)
+        a = rng.standard_normal((2, 2)) + 1j * rng.standard_normal((2, 2))
+        q, _ = np.linalg.qr(a)
+        m = np.array(qs.UnivGate.X) if i % 5 == 0 else q
+        mixed.add_raw([int(bits[0])], (1 << int(bits[1])) | (1 << int(bits[2])), 1 << int(bits[1]), m)
+    for prog in (qft_program(n), mixed):
+        x = rng.standard_normal((1 << n, 1)) + 1j * rng.standard_normal((1 << n, 1))
+        x /= np.linalg.norm(x)
+        first = apply_circuit(prog, x, fuse=True)
+        for _ in range(4):
+            assert np.array_equal(apply_circuit(prog, x, fuse=True), first)
+        ref = x[:, 0].copy()
+        orc.run_records(prog.records(0), prog.pool(), ref, n)
+        assert np.abs(first[:, 0] - ref).max() < TOL128
