@@ -213,3 +213,40 @@ def test_requested_end_layout(n, tile, carry):
         want = np.empty_like(ref)
         want[phys] = ref
         assert np.abs(got - want).max() < 1e-12, (case, final)
+
+
+def test_fuzz_random_programs_with_requested_layouts():
+    """Random programs over every op kind (tools/fuzz_fused.py) through the commuting-gate scheduler, the radix-8 generic
+    loop and -- every other case -- a requested end layout with or without an exchange-carrying last sweep."""
+    import importlib.util
+    import os
+    from oracle import sv_oracle
+    from tests.hostcheck import run_fused_to_layout_on_host
+    spec = importlib.util.spec_from_file_location("fuzz_fused", os.path.join(ROOT, "tools", "fuzz_fused.py"))
+    fz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fz)
+    rng = np.random.default_rng(11)
+    for case in range(24):
+        n = int(rng.integers(10, 15))
+        prog = fz.random_program(rng, n, int(rng.choice([5, 30, 120, 300])))
+        x = rng.standard_normal(1 << n) + 1j * rng.standard_normal(1 << n)
+        x /= np.linalg.norm(x)
+        ref = x.copy()
+        sv_oracle.run_records(prog.records(0), prog.pool(), ref, n)
+        tile = int(rng.choice([9, 10, 11]))
+        final = list(range(n))
+        if case % 2:
+            v = sorted(rng.choice(n, size=2, replace=False).tolist())
+            rest = [b for b in range(n) if b not in v]
+            for i, b in enumerate(rest):
+                final[b] = i
+            for i, b in enumerate(v):
+                final[b] = n - 2 + i
+        got, _, _ = run_fused_to_layout_on_host(prog.records(0), prog.pool(), x, n, final, bool(case % 3 == 0), tile)
+        idx = np.arange(1 << n)
+        phys = np.zeros_like(idx)
+        for b in range(n):
+            phys |= ((idx >> b) & 1) << final[b]
+        want = np.empty_like(ref)
+        want[phys] = ref
+        assert np.abs(got - want).max() < 1e-12, (case, n, tile, final)
