@@ -319,3 +319,39 @@ def test_trace_argument_errors():
     with pytest.raises(AssertionError) as e:
         g.trace(qs.Qubit(10), np.array([1, 0]))
     assert str(e.value) == 'Qubit q10 not in qspace.'
+
+
+def test_column_at_a_time_givens_producer_matches_the_sequential_one():
+    """two_level_stream_scan (closed form per QR column: prefix norms + one cumulative sum over the rows, torch; the GPU
+    producer of config 4) against two_level_stream (one rotation at a time, itself pinned to the reference's
+    mat2l_decompose by tests/golden/two_level.npz): same rotations in the same order to 1e-12, skip rules included."""
+    from quantum_simulations_b200.utils.mgen import cyclic_matrix, random_unitary
+    from quantum_simulations_b200.utils.producers import two_level_stream, two_level_stream_scan
+    np.random.seed(3)
+    cases = [random_unitary(n) for n in (3, 6, 8, 32, 64)]
+    cases += [np.array(cyclic_matrix(8, 1), dtype=complex), np.array(cyclic_matrix(16, 2), dtype=complex), np.eye(8, dtype=complex),
+              np.kron(np.eye(2), random_unitary(4)), np.kron(random_unitary(4), np.eye(2))]
+    d = __import__("tests.golden_io", fromlist=["load"]).load("two_level")
+    cases += [d[k] for k in d.files if k.endswith("_input")]
+    for u in cases:
+        a, b = two_level_stream(u), two_level_stream_scan(u, "cpu")
+        assert [(x[0], x[1]) for x in a] == [(y[0], y[1]) for y in b]
+        for x, y in zip(a, b):
+            assert np.abs(x[2] - y[2]).max() < 1e-12
+
+
+def test_vectorised_singlet_records_match_the_loop():
+    from quantum_simulations_b200.utils.mgen import cyclic_matrix, random_unitary
+    from quantum_simulations_b200.utils.producers import singlet_records, singlet_records_fast, two_level_stream
+    np.random.seed(4)
+    for n, bb, u in [(3, 0, random_unitary(8)), (5, 5, random_unitary(32)), (6, 2, random_unitary(64)),
+                     (4, 0, np.array(cyclic_matrix(16, 2), dtype=complex))]:
+        st = two_level_stream(u)
+        r1, p1 = singlet_records(st, n, bb)
+        r2, p2 = singlet_records_fast(st, n, bb)
+        assert len(r1) == len(r2)
+        for f in ("kind", "n_targets", "ctrl_mask", "ctrl_value", "target_bits"):
+            assert np.array_equal(r1[f], r2[f]), f
+        m1 = [p1[int(o):int(o) + 4] for o, k in zip(r1["matrix_offset"], r1["kind"]) if k != _lib.PERMX]
+        m2 = [p2[int(o):int(o) + 4] for o, k in zip(r2["matrix_offset"], r2["kind"]) if k != _lib.PERMX]
+        assert np.array_equal(np.array(m1), np.array(m2))
