@@ -875,7 +875,10 @@ struct PlanStep {
     int img;                // kernel image that runs it: IMG_FFT / IMG_FFT8 (only OP_FSTAGE ops), IMG_LEAN (lean op set) or IMG_FULL
     uint64_t n_gates;       // source gates carried
     Sweep8Extra* tma;       // IMG_FFT8: how the TMA engine sees a tile on load / store (host copy, owned)
+    void* launch_cache;     // IMG_FFT8: kernel parameters and tensor maps of the last launch (qsv_sweep8.cu), reused while the buffers stay
 };
+
+void sweep8_free_cache(void* cache);  // qsv_sweep8.cu
 
 struct SweepPlan {
     std::vector<PlanStep> steps;
@@ -889,6 +892,7 @@ struct SweepPlan {
         for (auto& s : steps) {
             delete s.params;
             delete s.tma;
+            sweep8_free_cache(s.launch_cache);
         }
         if (d_aux) cudaFree(d_aux);
         for (auto e : ev) cudaEventDestroy(e);
