@@ -586,3 +586,34 @@ def test_fused_runs_repeat_bit_for_bit(tile_bits, monkeypatch):
         ref = x[:, 0].copy()
         orc.run_records(prog.records(0), prog.pool(), ref, n)
         assert np.abs(first[:, 0] - ref).max() < TOL128
+
+
+def test_one_plan_over_changing_buffers():
+    """The radix-8 launch keeps its parameter block and its two tensor maps per plan step between runs
+    (``csrc/qsv_sweep8.cu`` ``Sweep8Launch``); a run on OTHER buffers must re-encode the maps: one fused QFT plan run on
+    buffers (a, s), again on (a, s), then on (b, s), (s2, a) and back gives the oracle's result every time."""
+    import torch
+    from quantum_simulations_b200.engine import Engine
+    from quantum_simulations_b200.utils.mgen import qft_program
+    n = 15
+    prog = qft_program(n)
+    eng = Engine(0, np.complex128)
+    eng.upload(prog, 0)
+    assert eng.fuse() > 0
+    rng = np.random.default_rng(31)
+
+    def fresh():
+        x = rng.standard_normal(1 << n) + 1j * rng.standard_normal(1 << n)
+        x /= np.linalg.norm(x)
+        want = x.copy()
+        orc.run_records(prog.records(0), prog.pool(), want, n)
+        return x, want
+
+    bufs = [torch.empty(1 << n, dtype=torch.complex128, device="cuda:0") for _ in range(4)]
+    for state_i, spare_i in ((0, 1), (0, 1), (2, 1), (3, 0), (1, 2), (0, 1)):
+        x, want = fresh()
+        bufs[state_i].copy_(torch.from_numpy(x))
+        res = eng.run(bufs[state_i], bufs[spare_i])
+        torch.cuda.synchronize()
+        assert np.abs(res.cpu().numpy() - want).max() < TOL128
+    eng.close()
