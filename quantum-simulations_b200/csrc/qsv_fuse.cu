@@ -778,6 +778,7 @@ struct Builder {
         memset(&X, 0, sizeof(X));
         if (!build_tma(tile_pos, X.in)) return false;
         X.out = X.in;
+        for (int l = 0; l < k; ++l) X.out_pos[l] = (uint8_t)tile_pos[l];
         if (!out_pos_of_phys) return true;
         std::vector<int> out_at(k), order(k), rank_of(k);
         for (int l = 0; l < k; ++l) {
@@ -793,6 +794,7 @@ struct Builder {
             identity &= order[u] == u;
         }
         if (!build_tma(sorted_out, X.out)) return false;
+        for (int u = 0; u < k; ++u) X.out_pos[u] = (uint8_t)sorted_out[u];
         if (identity) return true;  // the tile keeps its order in shared memory; only the addresses differ
         X.permuting = 1;
         X.loc_perm = make_segmap(rank_of);
@@ -993,7 +995,8 @@ struct Builder {
                 if (pg[gi].kind != QSV_DIAG1) seen |= 1ull << pg[gi].target_bits[0];
             n_t = __builtin_popcountll(seen);
         }
-        // (a sweep whose store carries an exchange fans out over several peers: the cp.async images do that, the TMA store does not)
+        // (a sweep whose store carries an exchange fans out over several peers: in the radix-8 image its threads store the
+        // output-ordered tile themselves instead of the engine; QSV_NO_CARRY8 keeps such sweeps in the cp.async images -- A/B aid)
         // (FFT-shaped launches: up to six targets = two stages; generic ones may take a third stage, see push_sweep)
         // A sweep of swaps and phases only (multi-controlled X streams) is cheap per stage: measured faster in three radix-8
         // stages than in two or three radix-16 ones (cyclic shift, 2^30: 25.2 against 28.7 ms), so it may carry up to 9 targets.
@@ -1002,7 +1005,8 @@ struct Builder {
         static const int gen8_env = getenv("QSV_GEN8_MAX_TARGETS") ? atoi(getenv("QSV_GEN8_MAX_TARGETS")) : 0;
         const int gen8_max = gen8_env ? gen8_env : (dense ? 6 : 9);
         n_targets_cur = n_t;
-        const bool try8 = allow8 && !(last_flush && carry_exchange) && k < n && k >= 9 && k <= 11 && n_t >= 1 && n_t <= std::max(6, gen8_max) &&
+        static const bool no_carry8 = getenv("QSV_NO_CARRY8") != nullptr;
+        const bool try8 = allow8 && !(last_flush && carry_exchange && no_carry8) && k < n && k >= 9 && k <= 11 && n_t >= 1 && n_t <= std::max(6, gen8_max) &&
                           n_t != 4;
         if (try8) {
             const size_t steps0 = plan->steps.size(), aux0 = plan->aux.size();
@@ -1267,8 +1271,7 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
         }
         if (!rc) {
             // the exchange rides on an out-of-place store: if the last sweep is not one, a gate-free permuting sweep is added
-            const bool last_ok = !plan->steps.empty() && plan->steps.back().fused && plan->steps.back().out_of_place &&
-                                 plan->steps.back().img != IMG_FFT8;
+            const bool last_ok = !plan->steps.empty() && plan->steps.back().fused && plan->steps.back().out_of_place;
             rc = b.restore_layout(carry_exchange && !last_ok);
         }
         if (rc) {

@@ -19,7 +19,7 @@
 // fstage8_put thread by thread, and a permuting launch re-orders the tile before the store like the kernel's last stage.
 template <typename R>
 static int sweep8_emulate_host(qsv_ctx* ctx, const SweepParams& P, const Sweep8Extra& X, const std::vector<double>& auxv,
-                               const typename cplx_of<R>::type* src, typename cplx_of<R>::type* dst) {
+                               const typename cplx_of<R>::type* src, typename cplx_of<R>::type* dst, bool thread_store) {
     typedef typename cplx_of<R>::type C;
     const SweepDesc& D = P.d;
     const int k = D.k;
@@ -140,7 +140,26 @@ static int sweep8_emulate_host(qsv_ctx* ctx, const SweepParams& P, const Sweep8E
                     fstage8_put<C>(tile, swz128(seg_apply(bl, X.loc_perm)), X.boff_out[0], X.boff_out[1], X.boff_out[2], w);
                 }
         }
-        if (!engine_copy(X.out, seg_apply64x(t, D.out_glob), false, nullptr, dst)) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: TMA store box leaves the tensor");
+        if (thread_store) {
+            // an exchange-carrying launch: the threads store the output-ordered tile themselves (k_sweep8, D.xg branch) --
+            // slot tid + (j << tb) goes to the tile's base plus the output offset of every set bit of the slot number
+            const int tb = k - RB8;
+            const uint64_t gb = seg_apply64x(t, D.out_glob);
+            for (uint32_t tid = 0; tid < threads; ++tid) {
+                uint64_t off = 0;
+                for (int u = 0; u < tb; ++u)
+                    if ((tid >> u) & 1u) off |= 1ull << X.out_pos[u];
+                for (int j = 0; j < NREG8; ++j) {
+                    uint64_t y = gb | off;
+                    for (int q = 0; q < RB8; ++q)
+                        if ((j >> q) & 1) y |= 1ull << X.out_pos[tb + q];
+                    if (y >> D.n_bits) return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: exchange store leaves the shard");
+                    dst[y] = tile[swz128(tid) | ((uint32_t)j << tb)];
+                }
+            }
+        } else if (!engine_copy(X.out, seg_apply64x(t, D.out_glob), false, nullptr, dst)) {
+            return qsv_fail(ctx, QSV_E_INVALID, "hostcheck: TMA store box leaves the tensor");
+        }
     }
     return QSV_OK;
 }
@@ -272,7 +291,7 @@ static int sweep_emulate_host(qsv_ctx* ctx, const SweepParams& P, const std::vec
 }
 
 template <typename R>
-static int hostcheck_run(qsv_ctx* ctx, SweepPlan* plan, void* state, uint64_t* out_sweeps, uint64_t* out_fft_sweeps) {
+static int hostcheck_run(qsv_ctx* ctx, SweepPlan* plan, void* state, uint64_t* out_sweeps, uint64_t* out_fft_sweeps, bool carry) {
     typedef typename cplx_of<R>::type C;
     const size_t amps = (size_t)1 << ctx->prog_bits;
     std::vector<C> spare_v(amps);
@@ -282,7 +301,7 @@ static int hostcheck_run(qsv_ctx* ctx, SweepPlan* plan, void* state, uint64_t* o
     for (auto& st : plan->steps) {
         if (!st.fused) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "hostcheck: the plan holds a gate that is not fused (dense-k / row pair)");
         C* d = st.out_of_place ? other : cur;
-        int rc = st.img == IMG_FFT8 ? sweep8_emulate_host<R>(ctx, *st.params, *st.tma, plan->aux, cur, d)
+        int rc = st.img == IMG_FFT8 ? sweep8_emulate_host<R>(ctx, *st.params, *st.tma, plan->aux, cur, d, carry && &st == &plan->steps.back())
                                     : sweep_emulate_host<R>(ctx, *st.params, plan->aux, st.img, cur, d);
         if (rc) return rc;
         if (st.out_of_place) std::swap(cur, other);
@@ -331,7 +350,7 @@ extern "C" int qsv_hostcheck_fused_layout(int dtype, int n_bits, const qsv_gate_
         ctx.prog_bits = n_bits;
         ctx.has_program = true;
         rc = sweep_plan_build_host(&ctx, max_tile_bits, &plan, final_pos, carry_exchange != 0);
-        if (!rc && carry_exchange && (plan->steps.empty() || !plan->steps.back().out_of_place || plan->steps.back().img == IMG_FFT8))
+        if (!rc && carry_exchange && (plan->steps.empty() || !plan->steps.back().out_of_place))
             rc = qsv_fail(&ctx, QSV_E_INVALID, "hostcheck: the plan's last sweep cannot carry an exchange");
     }
     if (!rc && !state) {
@@ -343,8 +362,8 @@ extern "C" int qsv_hostcheck_fused_layout(int dtype, int n_bits, const qsv_gate_
         if (out_sweeps) *out_sweeps = sweeps;
         if (out_fft_sweeps) *out_fft_sweeps = fft;
     } else if (!rc) {
-        rc = dtype == QSV_C128 ? hostcheck_run<double>(&ctx, plan, state, out_sweeps, out_fft_sweeps)
-                               : hostcheck_run<float>(&ctx, plan, state, out_sweeps, out_fft_sweeps);
+        rc = dtype == QSV_C128 ? hostcheck_run<double>(&ctx, plan, state, out_sweeps, out_fft_sweeps, carry_exchange != 0)
+                               : hostcheck_run<float>(&ctx, plan, state, out_sweeps, out_fft_sweeps, carry_exchange != 0);
     }
     if (plan) sweep_plan_free(plan);
     if (err && err_len) {

@@ -279,7 +279,8 @@ void sweep_plan_count(const SweepPlan* plan, uint64_t* sweeps, uint64_t* out_of_
 static int sweep_set_smem_attr(qsv_ctx* ctx, int k);
 // qsv_sweep8.cu: the radix-8 / TMA image
 int sweep8_prepare(qsv_ctx* ctx, int k);
-int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const double* d_aux, const PlanStep& st, cudaStream_t stream);
+int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const double* d_aux, const PlanStep& st, cudaStream_t stream, int xg,
+                  int xrank, const uint64_t* peers);
 
 int sweep_plan_build(qsv_ctx* ctx, int max_tile_bits, uint64_t* out_sweeps, const int* final_pos, bool carry_exchange) {
     SweepPlan* plan = nullptr;
@@ -402,13 +403,13 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
     void* cur = state;
     void* other = spare;
     if (xg > 0) {
-        if (plan->steps.empty() || !plan->steps.back().fused || !plan->steps.back().out_of_place || plan->steps.back().img == IMG_FFT8)
+        if (plan->steps.empty() || !plan->steps.back().fused || !plan->steps.back().out_of_place)
             return qsv_fail(ctx, QSV_E_INVALID, "this plan was not built to carry an exchange (qsv_fuse_to_layout with carry_exchange)");
     }
     for (auto& st : plan->steps) {
         const bool carries = xg > 0 && &st == &plan->steps.back();
         SweepParams* patched = nullptr;
-        if (carries) {
+        if (carries && st.img != IMG_FFT8) {
             // the last sweep's store goes to the peers: same launch, destination table filled in
             patched = new SweepParams(*st.params);
             patched->d.xg = xg;
@@ -432,7 +433,7 @@ int sweep_plan_run(qsv_ctx* ctx, void* state, void* spare, int* result_in_spare,
             QSV_CUDA(ctx, cudaEventRecord(ev0, stream));
         }
         {
-            int rc = st.img == IMG_FFT8 ? sweep8_launch(ctx, n, k, cur, dstp, plan->d_aux, st, stream)
+            int rc = st.img == IMG_FFT8 ? sweep8_launch(ctx, n, k, cur, dstp, plan->d_aux, st, stream, carries ? xg : 0, xrank, peers)
                                         : sweep_launch(ctx, n, k, cur, dstp, plan->d_aux, patched ? *patched : *st.params, stream, st.img);
             delete patched;
             if (rc) return rc;

@@ -52,6 +52,9 @@ struct Sweep8Params {
     int mid_layout;           // two-stage permuting launch through the intermediate swz() layout (Sweep8Extra)
     SegMap tmap_last;
     uint16_t boff_mid_w[RB8], boff_last_r[RB8];
+    // d.xg > 0 (the store is the exchange, see SweepDesc): the tile, complete in OUTPUT order in shared memory, is not
+    // handed to the engine but stored by the threads, each amplitude into the rank that owns it afterwards.
+    uint64_t x_bit_off[KMAX8];  // output index offset of bit u of the slot number (= the u-th lowest output tile bit)
 };
 
 namespace {
@@ -268,7 +271,7 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
         const bool more = tn > t && tn < n_tiles;
         if (tid == 0) {
             // the previous tile (other buffer) goes out, and as soon as the engine has read it the next one comes in
-            if (it) {
+            if (it && !D.xg) {
                 issue_store(t_prev, cur ^ 1);
                 asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             }
@@ -330,10 +333,34 @@ __global__ void __launch_bounds__(256, 3) k_sweep8(const __grid_constant__ CUten
                 if (i < n_ops - 1) __syncthreads();
             }
         }
+        if (D.xg) {
+            // The store IS the exchange: the top xg bits of an amplitude's output index name the rank that owns it next, and
+            // this rank's id takes their place in the address there.  Slot l of the output-ordered tile is stored by thread
+            // l mod blockDim: a warp writes 512 contiguous bytes of one peer per instruction.
+            __syncthreads();
+            const int tb = D.k - RB8;
+            uint64_t x_tid_off = 0;  // where the thread's slots tid + (j << tb) go, less the j part (recomputed per tile: a
+            for (int u = 0; u < tb; ++u)  // value kept across the stages would cost the other launches a register pair)
+                if ((tid >> u) & 1u) x_tid_off |= P.x_bit_off[u];
+            const int sh = D.n_bits - D.xg;
+            const uint64_t lowmask = (1ull << sh) - 1ull, mine = (uint64_t)D.xrank << sh;
+            const uint64_t gb = seg_apply64x(t, D.out_glob) | x_tid_off;
+            const uint64_t o0 = P.x_bit_off[tb], o1 = P.x_bit_off[tb + 1], o2 = P.x_bit_off[tb + 2];
+            const uint32_t s0 = swz128(tid);
+            C w[NREG8];
+#pragma unroll
+            for (int j = 0; j < NREG8; ++j) w[j] = tile[s0 | ((uint32_t)j << tb)];
+#pragma unroll
+            for (int j = 0; j < NREG8; ++j) {
+                const uint64_t y = gb | ((j & 1) ? o0 : 0ull) | ((j & 2) ? o1 : 0ull) | ((j & 4) ? o2 : 0ull);
+                C* pd = reinterpret_cast<C*>(D.peer[y >> sh]);
+                pd[mine | (y & lowmask)] = w[j];
+            }
+        }
         fence_async_smem();  // this thread's tile writes are visible to the engine once it has passed the next barrier
     }
     __syncthreads();
-    if (tid == 0 && it) {
+    if (tid == 0 && it && !D.xg) {
         issue_store(t_prev, (it - 1) & 1);
         asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
@@ -405,7 +432,9 @@ struct Sweep8Launch {
 
 void sweep8_free_cache(void* cache) { delete static_cast<Sweep8Launch*>(cache); }
 
-int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const double* d_aux, const PlanStep& st, cudaStream_t stream) {
+// xg > 0: the launch carries the exchange (peers[0 .. 2^xg) = every rank's destination buffer, xrank = this rank).
+int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const double* d_aux, const PlanStep& st, cudaStream_t stream, int xg,
+                  int xrank, const uint64_t* peers) {
     if (ctx->dtype != QSV_C128 || !st.tma) return qsv_fail(ctx, QSV_E_INVALID, "internal: radix-8 launch without a TMA tile description");
     if (n - k > 31) return qsv_fail(ctx, QSV_E_UNSUPPORTED, "unsupported: %d tile-id bits (max 31)", n - k);
     const int threads = 1 << (k - RB8);
@@ -419,6 +448,9 @@ int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const 
             L->src = src;
             L->dst = dst;
         }
+        L->P.d.xg = xg;
+        L->P.d.xrank = xrank;
+        for (int i = 0; i < (xg > 0 ? 1 << xg : 0); ++i) L->P.d.peer[i] = peers[i];
         k_sweep8<<<L->grid, threads, smem, stream>>>(L->tm_in, L->tm_out, d_aux, L->P);
         QSV_CUDA(ctx, cudaGetLastError());
         return QSV_OK;
@@ -460,6 +492,10 @@ int sweep8_launch(qsv_ctx* ctx, int n, int k, const void* src, void* dst, const 
     occ = std::max(occ, 1);
     const uint64_t n_tiles = 1ull << (n - k);
     L->grid = (unsigned)std::min<uint64_t>(n_tiles, (uint64_t)sm_count * occ);
+    for (int u = 0; u < k; ++u) P->x_bit_off[u] = 1ull << X.out_pos[u];
+    P->d.xg = xg;
+    P->d.xrank = xrank;
+    for (int i = 0; i < (xg > 0 ? 1 << xg : 0); ++i) P->d.peer[i] = peers[i];
     mst.launch_cache = L;
     k_sweep8<<<L->grid, threads, smem, stream>>>(L->tm_in, L->tm_out, d_aux, L->P);
     QSV_CUDA(ctx, cudaGetLastError());

@@ -19,6 +19,7 @@
 #define MAX_SEG 12
 // Radix-8 image (IMG_FFT8, qsv_sweep8.cu): 3 register bits per stage, 8 amplitudes per thread, tiles moved by TMA
 #define RB8 3
+#define KMAX8 11         // largest tile of the radix-8 image (2^11 amplitudes = 256 threads x 8)
 #define NREG8 8
 #define MAX_OPS8 300     // ops per launch of the radix-8 image (kernel parameter space; an FFT-shaped launch is one op per stage)
 #define MAX_GSLOT8 16    // per-tile phase scalars per launch of the radix-8 image
@@ -189,6 +190,7 @@ struct Sweep8Extra {
     SegMap tmap_last;             // thread id -> input-local index of its register 0 in the last stage
     uint16_t boff_mid_w[RB8];     // swz() slot offset of the first stage's register bit q (its write side)
     uint16_t boff_last_r[RB8];    // swz() slot offset of the last stage's register bit q (its read side)
+    uint8_t out_pos[KMAX];         // index bit (output layout) of slot-number bit u of the tile as it leaves: ascending
 };
 
 // An op held in registers: header words + 64-byte payload (all accesses statically indexed).
