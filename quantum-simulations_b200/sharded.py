@@ -681,9 +681,18 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
     dist.all_reduce(tot)
     # one more, untimed, step with CUDA events around every plan step: where the time goes, and the NVLink rate
     timers = []
+    for eng_, fused_ in execu.engines.values():
+        if fused_:
+            eng_.set_profiling(True)
     dist.barrier()
     state, spare = circ.apply(state, spare, timers)
     torch.cuda.synchronize()
+    # this rank's fused sweeps one by one, per local segment in plan order (the last sweep of a carrying segment is the exchange)
+    sweeps_ms = {}
+    for key_, (eng_, fused_) in execu.engines.items():
+        if fused_:
+            sweeps_ms[str(key_)] = [round(v, 3) for v in eng_.sweep_profile()]
+            eng_.set_profiling(False)
     split = {}
     for kind, a, b in timers:
         split[kind] = split.get(kind, 0.0) + a.elapsed_time(b)
@@ -723,6 +732,12 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
         stage_out = torch.empty(amps, dtype=torch.complex128, device=dev)
         s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
         main = torch.cuda.current_stream()
+        piece = (256 << 20) // 16     # host copies in 256 MiB pieces: measured faster with both directions busy (profiles/r2x_pcie_probe.json)
+
+        def copy_in_pieces(dst_t, src_t):
+            for o in range(0, amps, piece):
+                dst_t[o:o + piece].copy_(src_t[o:o + piece], non_blocking=True)
+
         torch.cuda.synchronize()
         dist.barrier()
 
@@ -739,7 +754,7 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
                     with torch.cuda.stream(s_in):
                         if ev_taken is not None:
                             s_in.wait_event(ev_taken)
-                        stage_in.copy_(host_in, non_blocking=True)
+                        copy_in_pieces(stage_in, host_in)
                         ev_in = torch.cuda.Event()
                         ev_in.record(s_in)
                 if i > 0:
@@ -751,7 +766,7 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
                     ev_res.record(main)
                     with torch.cuda.stream(s_out):
                         s_out.wait_event(ev_res)
-                        host_out.copy_(stage_out, non_blocking=True)
+                        copy_in_pieces(host_out, stage_out)
                         ev_out = torch.cuda.Event()
                         ev_out.record(s_out)
             main.wait_stream(s_out)
@@ -814,7 +829,8 @@ def _run_sharded(B, args, n, steps, warmup, e2e_steps, rank, world, local_rank):
                           "frac": (sent / (x_ms * 1e-3) / 1e9 / 770.0) if x_ms > 0 else None},
                "ms_split_one_step": {"local_sweeps": float(sp_t[0]), "local_permutes": float(sp_t[1]), "exchanges": float(sp_t[2]),
                                      "segments_whose_last_sweep_is_the_exchange": float(sp_t[3]),
-                                     "sweeps_in_those_segments": int(getattr(circ, "carrying_sweeps", 0))},
+                                     "sweeps_in_those_segments": int(getattr(circ, "carrying_sweeps", 0)),
+                                     "rank0_sweep_ms_by_segment": sweeps_ms},
                "cpu_baseline": None, "e2e": e2e, "gpu_launches": int(tot[1]), "clocks": clocks,
                "check": check, "max_abs_err": check["max_abs_err"] if check else None}
     del state, spare, circ, execu, exch
