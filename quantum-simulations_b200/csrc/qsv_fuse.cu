@@ -778,7 +778,7 @@ struct Builder {
         memset(&X, 0, sizeof(X));
         if (!build_tma(tile_pos, X.in)) return false;
         X.out = X.in;
-        for (int l = 0; l < k; ++l) X.out_pos[l] = (uint8_t)tile_pos[l];
+        for (int l = 0; l < k && l < KMAX; ++l) X.out_pos[l] = (uint8_t)tile_pos[l];
         if (!out_pos_of_phys) return true;
         std::vector<int> out_at(k), order(k), rank_of(k);
         for (int l = 0; l < k; ++l) {
@@ -794,7 +794,7 @@ struct Builder {
             identity &= order[u] == u;
         }
         if (!build_tma(sorted_out, X.out)) return false;
-        for (int u = 0; u < k; ++u) X.out_pos[u] = (uint8_t)sorted_out[u];
+        for (int u = 0; u < k && u < KMAX; ++u) X.out_pos[u] = (uint8_t)sorted_out[u];
         if (identity) return true;  // the tile keeps its order in shared memory; only the addresses differ
         X.permuting = 1;
         X.loc_perm = make_segmap(rank_of);
@@ -995,8 +995,11 @@ struct Builder {
                 if (pg[gi].kind != QSV_DIAG1) seen |= 1ull << pg[gi].target_bits[0];
             n_t = __builtin_popcountll(seen);
         }
-        // (a sweep whose store carries an exchange fans out over several peers: in the radix-8 image its threads store the
-        // output-ordered tile themselves instead of the engine; QSV_NO_CARRY8 keeps such sweeps in the cp.async images -- A/B aid)
+        // (a sweep whose store carries an exchange fans out over several peers.  The cp.async images do that by default; the
+        // radix-8 image can too -- its threads then store the output-ordered tile themselves instead of the engine -- but
+        // such a sweep is bound by the wire, not by its stages: measured on 8 B200 the radix-8 version is no faster on QFT-30
+        // (2.93 against 2.90 ms) and 4 % slower on QFT-34 (46.7 against 44.8 ms), profiles/r2_ab_carry8.txt.  QSV_CARRY8=1
+        // selects it.)
         // (FFT-shaped launches: up to six targets = two stages; generic ones may take a third stage, see push_sweep)
         // A sweep of swaps and phases only (multi-controlled X streams) is cheap per stage: measured faster in three radix-8
         // stages than in two or three radix-16 ones (cyclic shift, 2^30: 25.2 against 28.7 ms), so it may carry up to 9 targets.
@@ -1005,7 +1008,7 @@ struct Builder {
         static const int gen8_env = getenv("QSV_GEN8_MAX_TARGETS") ? atoi(getenv("QSV_GEN8_MAX_TARGETS")) : 0;
         const int gen8_max = gen8_env ? gen8_env : (dense ? 6 : 9);
         n_targets_cur = n_t;
-        static const bool no_carry8 = getenv("QSV_NO_CARRY8") != nullptr;
+        static const bool no_carry8 = getenv("QSV_CARRY8") == nullptr;
         const bool try8 = allow8 && !(last_flush && carry_exchange && no_carry8) && k < n && k >= 9 && k <= 11 && n_t >= 1 && n_t <= std::max(6, gen8_max) &&
                           n_t != 4;
         if (try8) {

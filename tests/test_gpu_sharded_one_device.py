@@ -1,7 +1,7 @@
 """The sharded path's exchange kernels on ONE GPU: every rank is a thread of this process with its shard on cuda:0, and the
 "peer" buffers a rank stores into are the other threads' buffers on the same device.  The kernels cannot tell (a peer is an
 address), so the fused permute+exchange kernel (``qsv_permute_exchange``) and the compute sweep whose store is the exchange
-(``qsv_run_exchange``, both the cp.async image and the radix-8 image with thread stores) run on a single-GPU box, where
+(``qsv_run_exchange``, the cp.async image and -- ``QSV_CARRY8=1`` -- the radix-8 image with thread stores) run on a single-GPU box, where
 ``tests/test_gpu_sharded.py`` (real NVLink peers, NCCL) is skipped.  Checked against ``torch.fft.ifft`` and the oracle."""
 import threading
 
@@ -136,8 +136,8 @@ def test_qft_ranks_as_threads(world, n, restore):
 
 
 def test_carrying_sweep_images_agree(monkeypatch):
-    """The exchange-carrying sweep in the radix-8 image (thread stores of the output-ordered tile) against the cp.async
-    image (``QSV_NO_CARRY8``, read when the library first plans such a sweep -- hence a subprocess for the second run)."""
+    """The exchange-carrying sweep in the radix-8 image (thread stores of the output-ordered tile, ``QSV_CARRY8=1`` -- read
+    when the library first plans such a sweep, hence a subprocess for that run) against the default cp.async image."""
     import subprocess
     import sys
     import torch
@@ -150,9 +150,12 @@ def test_carrying_sweep_images_agree(monkeypatch):
     import tempfile
     with tempfile.TemporaryDirectory() as d:
         path = os.path.join(d, "got.pt")
-        env = dict(os.environ, QSV_NO_CARRY8="1")
-        subprocess.run([sys.executable, "-c", code, path], check=True, env=env, cwd=os.path.dirname(os.path.dirname(__file__)))
+        env = dict(os.environ, QSV_CARRY8="1", QSV_PLAN_DEBUG="1")
+        run = subprocess.run([sys.executable, "-c", code, path], check=True, env=env, capture_output=True, text=True,
+                             cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
         other = torch.load(path)
+    # (the radix-8 image did carry it: a permuting store of that image appears in the plans)
+    assert any("fft8-tma" in ln and "permuting store" in ln for ln in (run.stderr + run.stdout).splitlines())
     assert float((got - other).abs().max()) < 1e-14
 
 
