@@ -427,7 +427,9 @@ def run_single(args):
     e2e = None
     third = eng.empty(amps)
     if args.e2e_steps > 0:
-        fourth = eng.empty(amps) if other is not None else None
+        fourth = None
+        if other is not None and torch.cuda.mem_get_info()[0] > amps * 16 + (8 << 30):   # (a 32 GiB state: three buffers must do)
+            fourth = eng.empty(amps)
         piece = (256 << 20) // 16
 
         def copy_in_pieces(dst_t, src_t):
@@ -438,7 +440,7 @@ def run_single(args):
         host_out = torch.empty(amps, dtype=torch.complex128, pin_memory=True)
         host_in.copy_(cur)
         torch.cuda.synchronize()
-        free = [cur, other, third, fourth] if other is not None else [cur, third]
+        free = [b for b in (cur, other, third, fourth) if b is not None]
         s_h2d, s_run, s_d2h = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
 
         def pipeline(count):
@@ -490,7 +492,7 @@ def run_single(args):
         e2e_ms = t0.elapsed_time(t1) / args.e2e_steps
         e2e = {"value": n_gates / (e2e_ms / 1e3), "unit": "gates/s", "h2d_bytes_per_step": amps * 16, "d2h_bytes_per_step": amps * 16,
                "ms_per_step": e2e_ms, "steps": args.e2e_steps,
-               "note": "steps pipelined over 4 device buffers / 3 streams, copies in 256 MiB pieces: D2H of step i overlaps H2D + compute of step i+1"}
+               "note": f"steps pipelined over {len(free)} device buffers / 3 streams, copies in 256 MiB pieces: D2H of step i overlaps H2D + compute of step i+1"}
         del host_in, host_out, fourth
     # ---- correctness at this size (outside the timed region) ------------------------------------
     check = None
