@@ -1047,6 +1047,10 @@ struct Builder {
                 fold = true;
                 cur_targets = need;
             }
+            static const bool dbg = getenv("QSV_PLAN_DEBUG") != nullptr;
+            if (dbg)
+                fprintf(stderr, "[qsv] fold? targets %#llx need %#llx (%d bits, tile %d) -> %s\n", (unsigned long long)cur_targets,
+                        (unsigned long long)need, __builtin_popcountll(need), k, fold ? "yes" : "no");
         }
         choose_tile();
         Emit e;
