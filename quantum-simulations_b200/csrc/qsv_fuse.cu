@@ -140,6 +140,8 @@ struct Builder {
     uint64_t forced_mask() const { return (1ull << c_low) - 1ull; }
 
     int target_cap = 64;  // max butterfly targets per sweep (see sweep_plan_build_host: balanced sweeps)
+    // Mixed caps: the first n_small sweeps take at most six targets (the radix-8 / TMA image), the others base_cap.
+    int base_cap = 64, n_small = 0, flushes = 0;
     bool fits(uint64_t targets) const {
         return __builtin_popcountll(targets | forced_mask()) <= k && __builtin_popcountll(targets) <= target_cap;
     }
@@ -982,6 +984,16 @@ struct Builder {
     }
 
     int flush() {
+        const bool had_gates = !cur.empty();
+        const int rc = flush_sweep();
+        if (!rc && had_gates) {
+            ++flushes;
+            target_cap = flushes < n_small ? std::min(6, base_cap) : base_cap;
+        }
+        return rc;
+    }
+
+    int flush_sweep() {
         if (cur.empty()) {
             cur_targets = 0;
             return QSV_OK;
@@ -1257,12 +1269,14 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
     }
     static const bool no_sched = getenv("QSV_NO_SCHEDULE") != nullptr;  // A/B aid: keep the program order
     if (!no_sched) schedule_commuting_gates(ctx, k);
-    auto build = [&](int cap, SweepPlan** out) -> int {
+    auto build = [&](int cap, SweepPlan** out, int n_small = 0) -> int {
         SweepPlan* plan = new SweepPlan();
         plan->k = k;
         plan->aux.resize(2, 0.0);  // offset 0 reserved
         Builder b(ctx, plan, n, k);
-        b.target_cap = cap;
+        b.base_cap = cap;
+        b.n_small = n_small;
+        b.target_cap = n_small > 0 ? std::min(6, cap) : cap;
         static const bool no8 = getenv("QSV_NO_FFT8") != nullptr;  // A/B aid: keep every launch in the cp.async images
         b.allow8 = ctx->dtype == QSV_C128 && !no8;
         if (final_pos)
@@ -1290,6 +1304,7 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
         return QSV_OK;
     };
     SweepPlan* best = nullptr;
+    int best_cap = 64;
     {
         int rc = build(64, &best);
         if (rc) return rc;
@@ -1300,7 +1315,8 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
     static const char* cap_env = getenv("QSV_SWEEP_TARGETS");  // tuning aid: fixed cap, no search
     if (cap_env) {
         SweepPlan* p = nullptr;
-        if (build(atoi(cap_env), &p) == QSV_OK) {
+        const char* colon = strchr(cap_env, ':');  // "cap" or "cap:m" (first m sweeps held to six targets)
+        if (build(atoi(cap_env), &p, colon ? atoi(colon + 1) : 0) == QSV_OK) {
             delete best;
             best = p;
         }
@@ -1314,6 +1330,33 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
             }
             delete best;
             best = p;
+            best_cap = cap;
+        }
+        // Mixed caps.  When the balanced plan needs seven or more targets per sweep, none of its sweeps can take the radix-8 /
+        // TMA image; but often the FIRST m sweeps can be held to six targets without adding a launch (31 targets in 5 sweeps:
+        // 6+6+6+6+7 instead of 7+7+7+7+3).  A six-target radix-8 sweep is faster than a seven-target radix-16 one (11.9
+        // against 13.5 ms over 2^31 amplitudes), and the radix-16 image pays ~25 % extra on a plan's first sweep (tile rows
+        // 128 MB apart), which the TMA image does not.  Largest m that keeps the launch count wins.
+        static const bool no_mixed = getenv("QSV_MIXED_CAPS") == nullptr;  // (off until measured on the GPU)
+        auto n_fft8 = [](const SweepPlan* p) {
+            int c = 0;
+            for (auto& st : p->steps) c += st.fused && st.img == IMG_FFT8;
+            return c;
+        };
+        if (!no_mixed && best_cap >= 7 && best_cap < 64 && ctx->dtype == QSV_C128 && k >= 9 && k <= 11) {
+            for (int m = (int)best->steps.size() - 1; m >= 1; --m) {
+                SweepPlan* p = nullptr;
+                if (build(best_cap, &p, m) != QSV_OK) break;
+                if (getenv("QSV_PLAN_DEBUG"))
+                    fprintf(stderr, "[qsv] mixed caps: first %d sweeps <= 6 targets, others <= %d: %zu launches (%d radix-8) against %zu (%d)\n", m,
+                            best_cap, p->steps.size(), n_fft8(p), best->steps.size(), n_fft8(best));
+                if (p->steps.size() <= best->steps.size() && n_fft8(p) > n_fft8(best)) {
+                    delete best;
+                    best = p;
+                    break;
+                }
+                delete p;
+            }
         }
         // Tried and measured worse (profiles/r2_ab_generic8.txt), kept behind QSV_COST_MODEL=1: trading launches for cheaper
         // ones.  A sweep of at most six targets is eligible for the radix-8 / TMA image; for 96 random controlled dense gates
