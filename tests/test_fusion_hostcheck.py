@@ -250,3 +250,31 @@ def test_fuzz_random_programs_with_requested_layouts():
         want = np.empty_like(ref)
         want[phys] = ref
         assert np.abs(got - want).max() < 1e-12, (case, n, tile, final)
+
+
+def test_mixed_target_caps_plan(tmp_path):
+    """``QSV_MIXED_CAPS``: the first sweeps of a plan are held to six targets (radix-8 / TMA image) when that adds no launch
+    -- QFT-19 at 2^11-amplitude tiles becomes 6+6+7 instead of 7+7+5.  The switch is read once per process, hence a
+    subprocess; the emulated result is compared with the oracle there and the plan's shape here."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys, numpy as np\n"
+        "from quantum_simulations_b200.utils.mgen import qft_program\n"
+        "from tests.hostcheck import run_fused_on_host\n"
+        "from oracle import sv_oracle as orc\n"
+        "n = 19\n"
+        "prog = qft_program(n)\n"
+        "rng = np.random.default_rng(3)\n"
+        "x = rng.standard_normal(1 << n) + 1j * rng.standard_normal(1 << n); x /= np.linalg.norm(x)\n"
+        "got, sweeps, fft = run_fused_on_host(prog.records(0), prog.pool(), x, n, tile_bits=11)\n"
+        "want = x.copy(); orc.run_records(prog.records(0), prog.pool(), want, n)\n"
+        "print('RESULT', sweeps, fft, float(np.abs(got - want).max()))\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, QSV_MIXED_CAPS="1", QSV_PLAN_DEBUG="1", PYTHONPATH=root)
+    run = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, check=True)
+    sweeps, fft, err = [ln for ln in run.stdout.splitlines() if ln.startswith("RESULT")][0].split()[1:]
+    assert int(sweeps) == 3 and int(fft) == 3 and float(err) < 1e-12
+    images = [ln for ln in run.stderr.splitlines() if "sweep: image" in ln][-3:]
+    assert sum("fft8-tma" in ln for ln in images) == 2, images
