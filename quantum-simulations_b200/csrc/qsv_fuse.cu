@@ -1336,8 +1336,9 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
         // TMA image; but often the FIRST m sweeps can be held to six targets without adding a launch (31 targets in 5 sweeps:
         // 6+6+6+6+7 instead of 7+7+7+7+3).  A six-target radix-8 sweep is faster than a seven-target radix-16 one (11.9
         // against 13.5 ms over 2^31 amplitudes), and the radix-16 image pays ~25 % extra on a plan's first sweep (tile rows
-        // 128 MB apart), which the TMA image does not.  Largest m that keeps the launch count wins.
-        static const bool no_mixed = getenv("QSV_MIXED_CAPS") == nullptr;  // (off until measured on the GPU)
+        // 128 MB apart), which the TMA image does not.  Largest m that keeps the launch count wins.  Measured: QFT-31 on one
+        // B200 59.6 against 65.7 ms per step (profiles/r2_ab_mixed_caps.txt).
+        static const bool no_mixed = getenv("QSV_NO_MIXED_CAPS") != nullptr;  // A/B aid
         auto n_fft8 = [](const SweepPlan* p) {
             int c = 0;
             for (auto& st : p->steps) c += st.fused && st.img == IMG_FFT8;

@@ -253,9 +253,9 @@ def test_fuzz_random_programs_with_requested_layouts():
 
 
 def test_mixed_target_caps_plan(tmp_path):
-    """``QSV_MIXED_CAPS``: the first sweeps of a plan are held to six targets (radix-8 / TMA image) when that adds no launch
-    -- QFT-19 at 2^11-amplitude tiles becomes 6+6+7 instead of 7+7+5.  The switch is read once per process, hence a
-    subprocess; the emulated result is compared with the oracle there and the plan's shape here."""
+    """Mixed target caps: the first sweeps of a plan are held to six targets (radix-8 / TMA image) when that adds no launch
+    -- QFT-19 at 2^11-amplitude tiles becomes 6+6+7 instead of 7+7+5 (``QSV_NO_MIXED_CAPS`` restores the balanced plan).
+    The plan's shape is read from the debug output of a subprocess; the emulated result is compared with the oracle there."""
     import os
     import subprocess
     import sys
@@ -272,9 +272,11 @@ def test_mixed_target_caps_plan(tmp_path):
         "want = x.copy(); orc.run_records(prog.records(0), prog.pool(), want, n)\n"
         "print('RESULT', sweeps, fft, float(np.abs(got - want).max()))\n")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    env = dict(os.environ, QSV_MIXED_CAPS="1", QSV_PLAN_DEBUG="1", PYTHONPATH=root)
-    run = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, check=True)
-    sweeps, fft, err = [ln for ln in run.stdout.splitlines() if ln.startswith("RESULT")][0].split()[1:]
-    assert int(sweeps) == 3 and int(fft) == 3 and float(err) < 1e-12
-    images = [ln for ln in run.stderr.splitlines() if "sweep: image" in ln][-3:]
-    assert sum("fft8-tma" in ln for ln in images) == 2, images
+    for switch, n_radix8 in (({}, 2), ({"QSV_NO_MIXED_CAPS": "1"}, 1)):
+        env = dict(os.environ, QSV_PLAN_DEBUG="1", PYTHONPATH=root, **switch)
+        env.pop("QSV_NO_MIXED_CAPS", None) if not switch else None
+        run = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, check=True)
+        sweeps, fft, err = [ln for ln in run.stdout.splitlines() if ln.startswith("RESULT")][0].split()[1:]
+        assert int(sweeps) == 3 and int(fft) == 3 and float(err) < 1e-12
+        images = [ln for ln in run.stderr.splitlines() if "sweep: image" in ln][-3:]
+        assert sum("fft8-tma" in ln for ln in images) == n_radix8, images

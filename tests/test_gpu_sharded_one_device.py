@@ -150,7 +150,8 @@ def test_carrying_sweep_images_agree(monkeypatch):
     import tempfile
     with tempfile.TemporaryDirectory() as d:
         path = os.path.join(d, "got.pt")
-        env = dict(os.environ, QSV_CARRY8="1", QSV_PLAN_DEBUG="1")
+        # (QSV_NO_MIXED_CAPS: the balanced plan, whose carrying sweep has five targets -- eligible for the radix-8 image)
+        env = dict(os.environ, QSV_CARRY8="1", QSV_NO_MIXED_CAPS="1", QSV_PLAN_DEBUG="1")
         run = subprocess.run([sys.executable, "-c", code, path], check=True, env=env, capture_output=True, text=True,
                              cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
         other = torch.load(path)
