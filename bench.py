@@ -537,7 +537,7 @@ def main():
     ap.add_argument("--restore-layout", action="store_true",
                     help="sharded runs: bring the result back to the canonical layout (one more exchange per QFT) instead of "
                          "reporting the final bit-position table")
-    ap.add_argument("--e2e-steps", type=int, default=16)
+    ap.add_argument("--e2e-steps", type=int, default=32)
     ap.add_argument("--cpu-gates", type=int, default=12, help="gates in the CPU baseline sample (0 = skip)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "fused", "nccl"], help="multi-GPU exchange engine")
     ap.add_argument("--circuit", default="qft", help="qft | random:DEPTH[:SEED] | cyclic | hlayer:LO:HI (diagnostic)")
