@@ -140,8 +140,8 @@ struct Builder {
     uint64_t forced_mask() const { return (1ull << c_low) - 1ull; }
 
     int target_cap = 64;  // max butterfly targets per sweep (see sweep_plan_build_host: balanced sweeps)
-    // Mixed caps: the first n_small sweeps take at most small_cap targets (six: the radix-8 / TMA image), the others base_cap.
-    int base_cap = 64, n_small = 0, small_cap = 6, flushes = 0;
+    // Mixed caps: the first n_small sweeps take at most six targets (the radix-8 / TMA image), the others base_cap.
+    int base_cap = 64, n_small = 0, flushes = 0;
     bool fits(uint64_t targets) const {
         return __builtin_popcountll(targets | forced_mask()) <= k && __builtin_popcountll(targets) <= target_cap;
     }
@@ -988,7 +988,7 @@ struct Builder {
         const int rc = flush_sweep();
         if (!rc && had_gates) {
             ++flushes;
-            target_cap = flushes < n_small ? std::min(small_cap, base_cap) : base_cap;
+            target_cap = flushes < n_small ? std::min(6, base_cap) : base_cap;
         }
         return rc;
     }
@@ -1269,15 +1269,14 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
     }
     static const bool no_sched = getenv("QSV_NO_SCHEDULE") != nullptr;  // A/B aid: keep the program order
     if (!no_sched) schedule_commuting_gates(ctx, k);
-    auto build = [&](int cap, SweepPlan** out, int n_small = 0, int small_cap = 6) -> int {
+    auto build = [&](int cap, SweepPlan** out, int n_small = 0) -> int {
         SweepPlan* plan = new SweepPlan();
         plan->k = k;
         plan->aux.resize(2, 0.0);  // offset 0 reserved
         Builder b(ctx, plan, n, k);
         b.base_cap = cap;
         b.n_small = n_small;
-        b.small_cap = small_cap;
-        b.target_cap = n_small > 0 ? std::min(small_cap, cap) : cap;
+        b.target_cap = n_small > 0 ? std::min(6, cap) : cap;
         static const bool no8 = getenv("QSV_NO_FFT8") != nullptr;  // A/B aid: keep every launch in the cp.async images
         b.allow8 = ctx->dtype == QSV_C128 && !no8;
         if (final_pos)
@@ -1345,26 +1344,6 @@ int sweep_plan_build_host(qsv_ctx* ctx, int max_tile_bits, SweepPlan** out_plan,
             for (auto& st : p->steps) c += st.fused && st.img == IMG_FFT8;
             return c;
         };
-        // A plan whose last sweep carries an exchange: that sweep is bound by the wire, its stages are hidden, so the sweep
-        // that needs the plan's largest target count should be THAT one (QFT-30 on 2 GPUs: 7+7+7+8 instead of 8+7+7+7 --
-        // an eight-target sweep of the radix-16 image costs ~25 % more than a seven-target one).
-        if (!no_mixed && carry_exchange && best_cap >= 8 && best_cap < 64 && best->steps.size() >= 2) {
-            SweepPlan* p = nullptr;
-            if (build(best_cap, &p, (int)best->steps.size() - 1, best_cap - 1) == QSV_OK) {
-                const bool ok = p->steps.size() <= best->steps.size() && p->steps.back().fused && p->steps.back().out_of_place &&
-                                p->steps.back().params->d.n_ops > 0;
-                if (getenv("QSV_PLAN_DEBUG"))
-                    fprintf(stderr, "[qsv] largest sweep last (all but the last sweep <= %d targets): %zu launches against %zu -> %s\n", best_cap - 1,
-                            p->steps.size(), best->steps.size(), ok ? "taken" : "no");
-                if (ok) {
-                    delete best;
-                    best = p;
-                    best_cap = best_cap - 1;  // (what the mixed search below may still assume of the other sweeps)
-                } else {
-                    delete p;
-                }
-            }
-        }
         if (!no_mixed && best_cap >= 7 && best_cap < 64 && ctx->dtype == QSV_C128 && k >= 9 && k <= 11) {
             for (int m = (int)best->steps.size() - 1; m >= 1; --m) {
                 SweepPlan* p = nullptr;
